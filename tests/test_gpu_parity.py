@@ -152,7 +152,7 @@ def test_function_level_random_state_nonuniform_mass():
     array order unrelated to x (the sort path): ghosts, density (+counts), forces."""
     rng = np.random.default_rng(1234)
     n = 3000
-    kw = dict(n_part=n, mass=4.0 / n, pressure_calc=1, limit=2.0, v_0=1.0, h_factor=2.0, t_i=1e-4,
+    kw = dict(n_part=n, mass=4.0 / n, pressure_calc=1, limit=2.0, v_0=1.0, h_factor=2.0, t_i=2e-6,
               variable_h=True, constant_h=0.2)
     x = np.sort(rng.uniform(-1.9995, 1.9995, n))
     x += rng.normal(0, 1e-5, n)
@@ -160,7 +160,7 @@ def test_function_level_random_state_nonuniform_mass():
     f = np.zeros((n, 9))
     f[:, 0] = (4.0 / n) * rng.uniform(0.7, 1.3, n)
     f[:, 1] = x[perm]
-    f[:, 2] = rng.normal(0, 0.5, n)
+    f[:, 2] = 0.3 * np.sin(3 * f[:, 1]) + rng.normal(0, 0.01, n)
     f[:, 4] = 2.0 * 4.0 / n * rng.uniform(0.8, 1.5, n)
     f[:, 6] = rng.uniform(1.0, 2.0, n)
     f[:, 7] = 1.0
@@ -189,12 +189,15 @@ def test_function_level_random_state_nonuniform_mass():
     fo, fs = o.fields(), sim.fields()[0]
     for c in ("acc", "du_dt", "pressure"):
         assert scaled_err(fs[:n, COLS[c]], fo[:n, COLS[c]]) < 1e-9, c
-    # and an ordered step from there (array order != x order: the sweep is by index, F9)
-    # (a second step would abort in the reference: a bisection bracket without a sign change)
-    o.step(1)
-    sim.step(1)
-    fo, fs = o.fields(), sim.fields()[0]
-    _compare(fs, fo, n, True, "random state, 1 step")
+    # and a few ordered steps from there (array order != x order: the sweep is by index, F9)
+    for st in (1, 2, 3):
+        o.step(1)
+        sim.step(1)
+        fo, (fs, _, ng) = o.fields(), sim.fields()
+        assert ng == o.n_ghost
+        assert np.isfinite(fo).all()
+        _compare(fs, fo, n, True, "random state, step %d" % st)
+    assert sim.counters().fallbacks == o.fallback_count()
     sim.close()
 
 
