@@ -156,6 +156,23 @@ int sphb_set_profiling(sphb_handle *h, int on);
 /* ms[p], launches[p] accumulated since the last reset; reset != 0 clears them */
 int sphb_get_phase_times(sphb_handle *h, double *ms, long long *launches, int reset);
 
+/* No counterpart in the reference.  The same density / root-find / omega pass as sphb_density,
+ * for callers that cannot allocate device memory when they need it (the whole device already
+ * belongs to their own arena allocator, or they are inside a section where cudaMalloc's
+ * device-wide synchronisation is not acceptable).  No handle: d_x (ascending), d_h, d_rho are
+ * device arrays of n particles of equal `mass` with no ghosts; results go to d_h_out, d_rho_out
+ * (device, n each; for variable_h = 0 only d_rho_out changes meaningfully, d_h_out = d_h).
+ * Scratch is a fixed device array inside the library, so n <= SPHB_STATIC_MAX_PARTICLES
+ * (larger n returns SPHB_ERR_CAPACITY and launches nothing), every call shares it, and calls
+ * that overlap on the GPU race: serialise them.  The first call on a device resolves the
+ * array's address; make it before any stream capture.  Synchronises `cuda_stream`
+ * (NULL = the default stream) and returns 0 or the first device-side error code; the text
+ * is read with sphb_last_error(NULL).  Calls no cudaMalloc / cudaFree. */
+#define SPHB_STATIC_MAX_PARTICLES (1 << 20)
+int sphb_density_static(const double *d_x, const double *d_h, const double *d_rho, int n, double mass,
+                        double h_factor, double limit, int variable_h, double *d_h_out, double *d_rho_out,
+                        void *cuda_stream);
+
 /* library identity: returns the compiled-for architecture string, e.g. "sm_100a" */
 const char *sphb_build_arch(void);
 

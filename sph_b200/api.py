@@ -139,10 +139,25 @@ def load_library():
     L.sphb_get_config.argtypes = [p, C.POINTER(SphbConfig)]
     L.sphb_set_profiling.argtypes = [p, i]
     L.sphb_get_phase_times.argtypes = [p, C.POINTER(d), C.POINTER(C.c_longlong), i]
+    L.sphb_density_static.argtypes = [p, p, p, i, d, d, d, i, p, p, p]
     L.sphb_build_arch.argtypes = []
     L.sphb_build_arch.restype = C.c_char_p
     _lib = L
     return L
+
+
+STATIC_MAX_PARTICLES = 1 << 20   # SPHB_STATIC_MAX_PARTICLES, include/sphb.h
+
+
+def density_static(d_x, d_h, d_rho, n, mass, h_factor, limit, variable_h, d_h_out, d_rho_out, stream=0):
+    """sphb_density_static: the handle-less density pass that allocates nothing.  Arguments are
+    raw device addresses (ints) of n-element double arrays owned by the caller."""
+    L = load_library()
+    rc = L.sphb_density_static(C.c_void_p(d_x), C.c_void_p(d_h), C.c_void_p(d_rho), int(n), float(mass),
+                               float(h_factor), float(limit), int(variable_h), C.c_void_p(d_h_out),
+                               C.c_void_p(d_rho_out), C.c_void_p(stream))
+    if rc != 0:
+        raise SphbError(rc, L.sphb_last_error(None).decode())
 
 
 def exported_symbols() -> list:

@@ -776,4 +776,91 @@ int sphb_get_phase_times(sphb_handle *H, double *ms, long long *launches, int re
     return SPHB_OK;
 }
 
+
+// ------------------------------------------------------------------------------------
+// sphb_density_static — the density / root-find / omega pass for callers that must not
+// allocate.  It has no counterpart in the reference.
+//
+// Some hosts of this library cannot call cudaMalloc at the point where they need a
+// density pass: applications that hand the whole device to their own arena allocator at
+// start-up (a later cudaMalloc simply fails there), and code inside a latency-critical
+// section where cudaMalloc's device-wide synchronisation would stall every other stream.
+// Every other entry point needs a handle, and sphb_create allocates.  This one needs no
+// handle: the caller passes device pointers for inputs and outputs, and the per-particle
+// work arrays k_density writes besides its outputs (omega of the new and of the old
+// state, packed iteration / neighbour counts) plus the control block live in ONE
+// file-scope device array of fixed size, which every GPU that loads libsphb.so keeps
+// until the process exits (20 MiB + 256 B).
+//
+// Rules that follow from the shared array:
+//   * n is limited to SPHB_STATIC_MAX_PARTICLES; larger calls are refused, nothing runs.
+//   * The array keeps what the previous call left in it.  The control block (error word,
+//     fallback counter, h maximum) is cleared on the stream at the start of every call;
+//     the work arrays are fully rewritten for [0, n) before anything reads them.
+//   * Two calls whose device work overlaps (different streams, or different host threads)
+//     race on the array.  Serialise them.
+//   * The first call on each device looks up the array's device address
+//     (cudaGetSymbolAddress with that device current).  Make that first call before
+//     starting any stream capture.
+// No cudaMalloc / cudaFree / allocating library routine is called on this path.
+namespace {
+constexpr size_t kStaticCtlBytes = 256;
+constexpr size_t kStaticBytes = kStaticCtlBytes + (size_t)SPHB_STATIC_MAX_PARTICLES * (8 + 8 + 4);
+// In host code this name is only a stand-in for the symbol: it is NOT a device address.
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+constexpr int kMaxDevices = 64;
+unsigned char *g_static_ptr[kMaxDevices] = {};   // device address of g_static_scratch, per device
+std::string g_static_err;
+}  // namespace
+
+int sphb_density_static(const double *d_x, const double *d_h, const double *d_rho, int n, double mass,
+                        double h_factor, double limit, int variable_h, double *d_h_out, double *d_rho_out,
+                        void *cuda_stream) {
+    sphb_handle *H = &g_null_handle_for_errors;   // error text is read with sphb_last_error(NULL)
+    if (!d_x || !d_h || !d_rho || !d_h_out || !d_rho_out || n < 1) { H->err = "sphb_density_static: null pointer or n < 1"; return SPHB_ERR_INVALID; }
+    if (n > SPHB_STATIC_MAX_PARTICLES) {
+        char b[200];
+        snprintf(b, sizeof b, "sphb_density_static: n = %d exceeds SPHB_STATIC_MAX_PARTICLES = %d (the static scratch "
+                 "array is fixed-size; use sphb_density on a handle for larger sets)", n, SPHB_STATIC_MAX_PARTICLES);
+        H->err = b;
+        return SPHB_ERR_CAPACITY;
+    }
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) { H->err = "sphb_density_static: device ordinal out of range"; return SPHB_ERR_INVALID; }
+    if (!g_static_ptr[dev]) {
+        // once per device, with that device current: the symbol's address ON THIS DEVICE
+        void *p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_static_scratch));
+        g_static_ptr[dev] = (unsigned char *)p;
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    unsigned char *base = g_static_ptr[dev];
+    Ctl *ctl = (Ctl *)base;
+    double *om_new = (double *)(base + kStaticCtlBytes);
+    double *om_stale = om_new + SPHB_STATIC_MAX_PARTICLES;
+    int *cnt = (int *)(om_stale + SPHB_STATIC_MAX_PARTICLES);
+    CK(cudaMemsetAsync(ctl, 0, sizeof(Ctl), st));   // GL = GR = 0 (no ghosts), no error, hmax = 0
+    DensityArgs A;
+    A.x = d_x; A.m = nullptr; A.h = d_h; A.rho = d_rho; A.P = nullptr;
+    A.hn = d_h_out; A.rhon = d_rho_out; A.omn = om_new; A.oms = om_stale; A.Pn = nullptr;
+    A.cnt = cnt; A.ctl = ctl; A.pad = 0; A.na = n;
+    A.limit = limit; A.hfac = h_factor; A.m0 = mass;
+    A.root_ghosts = 0; A.root_alive = 1; A.check_old = 0;
+    const int grid = nblk(n, kTile);
+    if (variable_h) k_density<true, true><<<grid, kTile, 0, st>>>(A);
+    else k_density<false, true><<<grid, kTile, 0, st>>>(A);
+    CK(cudaGetLastError());
+    Ctl host_ctl;   // pageable stack memory: the copy allocates nothing
+    CK(cudaMemcpyAsync(&host_ctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (host_ctl.err_code != 0) {
+        char b[256];
+        snprintf(b, sizeof b, "%s (particle %d)", err_text(host_ctl.err_code), host_ctl.err_particle);
+        H->err = b;
+        return host_ctl.err_code;
+    }
+    return SPHB_OK;
+}
+
 }  // extern "C"
