@@ -138,6 +138,10 @@ int sphb_density(sphb_handle *h, int include_ghosts);
  * (calculators.cpp:63-129,192-213) for every alive particle, no kick
  * (the order-independent t = 0 pass, setup.cpp:223-226). */
 int sphb_forces(sphb_handle *h);
+/* Replaces calc_omega (smoothing_length.cpp:64-77) for every particle, ghosts included:
+ * omega[i] = 1 + (h_i / rho_i) sum_j m_j dW/dh at the particle's STORED h and density and the
+ * current positions (1 for fixed h); array-index order.  Nothing of the state changes. */
+int sphb_omega(sphb_handle *h, double *omega, int cap);
 /* Replaces setup_ghost_particles (ghost_particles.cpp:19-115). */
 int sphb_ghosts(sphb_handle *h, int *n_ghost);
 /* Replaces the first loop of SPHSimulation::step_forward (sph_simulation.cpp:59-73). */

@@ -132,6 +132,7 @@ def load_library():
     L.sphb_init_lattice.argtypes = [p]
     L.sphb_density.argtypes = [p, i]
     L.sphb_forces.argtypes = [p]
+    L.sphb_omega.argtypes = [p, p, i]
     L.sphb_ghosts.argtypes = [p, ip]
     L.sphb_kick_drift.argtypes = [p]
     L.sphb_step.argtypes = [p, i]
@@ -254,6 +255,11 @@ class Simulation:
 
     def forces(self):
         self._check(self.L.sphb_forces(self.h))
+
+    def omega(self):
+        out = np.zeros(self._cap, dtype=np.float64)
+        self._check(self.L.sphb_omega(self.h, out.ctypes.data, self._cap))
+        return out[: self.counters().n_alive + self.counters().n_ghost].copy()
 
     def ghosts(self) -> int:
         g = C.c_int()

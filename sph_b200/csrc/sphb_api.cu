@@ -671,6 +671,23 @@ int sphb_forces(sphb_handle *H) {
     return read_ctl(H);
 }
 
+int sphb_omega(sphb_handle *H, double *omega, int cap) {
+    if (!H || !omega) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    TRY(ghosts_to_current(H));
+    TRY(launch_begin(H, 0));
+    TRY(launch_density(H, 0, 0, 0, H->P));   // omega only: h, density stay as stored
+    TRY(read_ctl(H));
+    const int n = H->na + H->h_ctl->GL + H->h_ctl->GR;
+    if (n > cap) { H->err = "download buffer too small"; return SPHB_ERR_CAPACITY; }
+    k_pack_f64<<<nblk(n, 256), 256, 0, H->stream>>>(H->omn, H->tmp, H->idx, H->gorder, H->d_ctl, H->pad, H->na);
+    H->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(omega, H->tmp, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaStreamSynchronize(H->stream));
+    return SPHB_OK;
+}
+
 int sphb_step(sphb_handle *H, int nsteps) {
     if (!H || nsteps < 0) return SPHB_ERR_INVALID;
     CK(cudaSetDevice(H->device));

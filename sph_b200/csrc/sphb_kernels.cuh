@@ -736,6 +736,20 @@ __global__ void k_pack(PackArgs A) {
     }
 }
 
+// one double per particle, sorted slot -> array-index order (same mapping as k_pack)
+__global__ void k_pack_f64(const double *src, double *out, const unsigned *idx, const int *gorder, const Ctl *ctl,
+                           int pad, int na) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int ng = ctl->GL + ctl->GR;
+    if (t >= na + ng) return;
+    if (t < na) {
+        const int s = pad + t;
+        out[idx[s]] = src[s];
+    } else {
+        out[t] = src[gorder[t - na]];
+    }
+}
+
 // ------------------------------------------------------------------------------------
 // sort support
 __global__ void k_iota(int *p, int n) {

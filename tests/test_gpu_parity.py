@@ -181,6 +181,8 @@ def test_function_level_random_state_nonuniform_mass():
     nw, nb = sim.counts()
     assert_neighbour_counts(nb, o.neighbour_counts(), fo, nt, "random state")
     assert np.array_equal(nw[:nt], o.newton_iters()[:nt])
+    # calc_omega for every particle's stored (h, density), ghosts included
+    assert scaled_err(sim.omega()[:nt], o.omega()[:nt]) < TOL
     # this rough state defeats Newton for a third of the particles: the bisection fallback
     # (smoothing_length.cpp:134-188) is exercised, equally often on both sides
     assert o.fallback_count() > 100 and sim.counters().fallbacks == o.fallback_count()
