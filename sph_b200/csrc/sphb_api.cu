@@ -198,6 +198,9 @@ int sort_alive(sphb_handle *H, bool full) {
         TRY(gather_f64(H, H->v)); TRY(gather_f64(H, H->u)); TRY(gather_f64(H, H->a)); TRY(gather_f64(H, H->du));
     } else {
         TRY(gather_f64(H, H->vh)); TRY(gather_f64(H, H->uh));
+        // a, du of the alive block are rewritten by the force pass, but the ghost copies made
+        // right after this sort take them from their source's slot (ghost_particles.cpp:53,111)
+        TRY(gather_f64(H, H->a)); TRY(gather_f64(H, H->du));
     }
     TRY(gather_f64(H, H->h)); TRY(gather_f64(H, H->rho)); TRY(gather_f64(H, H->P)); TRY(gather_f64(H, H->m));
     k_gather_u32<<<nblk(H->na, 256), 256, 0, H->stream>>>(H->idx, H->idx_alt, H->perm, H->pad, H->na);

@@ -45,7 +45,14 @@ def _compare(f, ref, na, adiabatic, what, tol=TOL, cols=None):
 
 def _compare_ghosts(f, ref, na, what, t0):
     # ghosts are copies: position mirrored, velocity negated, the rest as the source had it
-    cols = ["pos", "vel", "h", "u", "density", "mass"]
+    cols = ["pos", "vel", "h", "u", "density", "mass", "pressure"]
+    if not t0:
+        # at t = 0 the reference's ghost records carry dead values: the acceleration of the adiabatic
+        # pre-pass (setup.cpp:192-202) and a du/dt evaluated at the mirrored position (:223-226).
+        # sphb_init_lattice does not reproduce those two (nothing ever reads them; the functor
+        # route of the C++ adaptors does, see tests/test_dropin_binary.py); from step 1 on they
+        # are copies of the source's values and are compared.
+        cols += ["acc", "du_dt"]
     for c in cols:
         e = scaled_err(f[na:, COLS[c]], ref[na:, COLS[c]])
         assert e < TOL, "%s: ghost %s differs by %.3e" % (what, c, e)
