@@ -35,7 +35,8 @@ struct sphb_handle {
            *rhon = nullptr, *omn = nullptr, *oms = nullptr, *Pn = nullptr, *tmp = nullptr;
     unsigned *idx = nullptr, *idx_alt = nullptr;
     int *slot_id = nullptr, *cnt = nullptr, *dirty = nullptr, *cand = nullptr, *gorder = nullptr,
-        *perm = nullptr, *iota = nullptr;
+        *perm = nullptr, *iota = nullptr, *wl0 = nullptr, *wl1 = nullptr;
+    Rec *recA = nullptr, *recB = nullptr;   // force-pass records written by the density pass
     // ghost staging (2*pad each)
     double *gx = nullptr, *gv = nullptr, *gu = nullptr, *ga = nullptr, *gdu = nullptr, *gh = nullptr,
            *grho = nullptr, *gP = nullptr, *gm = nullptr;
@@ -227,10 +228,13 @@ int launch_ghost_build(sphb_handle *H, int from_alive, int nstaged, double *vs, 
     return SPHB_OK;
 }
 
-int launch_density(sphb_handle *H, int root_alive, int root_ghosts, int check_old, double *Pn) {
+int launch_density(sphb_handle *H, int root_alive, int root_ghosts, int check_old, double *Pn,
+                   bool want_omega = false) {
     DensityArgs A;
     A.x = H->x; A.m = H->m; A.h = H->h; A.rho = H->rho; A.P = H->P;
-    A.hn = H->hn; A.rhon = H->rhon; A.omn = H->omn; A.oms = H->oms; A.Pn = Pn;
+    A.hn = H->hn; A.rhon = H->rhon; A.Pn = Pn;
+    A.omn = want_omega ? H->omn : nullptr; A.oms = want_omega ? H->oms : nullptr;
+    A.recA = H->recA; A.recB = H->recB;
     A.cnt = H->cnt; A.ctl = H->d_ctl; A.pad = H->pad; A.na = H->na;
     A.limit = H->cfg.limit; A.hfac = H->cfg.h_factor; A.m0 = H->m0;
     A.root_ghosts = root_ghosts; A.root_alive = root_alive; A.check_old = check_old;
@@ -283,7 +287,8 @@ int launch_refine(sphb_handle *H, SweepArgs A) {
 SweepArgs sweep_args(sphb_handle *H) {
     SweepArgs A;
     A.F.x = H->x; A.F.idx = H->idx; A.F.m = H->m;
-    A.a = H->a; A.du = H->du; A.dirty = H->dirty; A.ctl = H->d_ctl;
+    A.F.recA = H->recA; A.F.recB = H->recB;
+    A.a = H->a; A.du = H->du; A.dirty = H->dirty; A.wl[0] = H->wl0; A.wl[1] = H->wl1; A.ctl = H->d_ctl;
     A.pad = H->pad; A.na = H->na; A.m0 = H->m0; A.half_dt = H->cfg.t_i / 2;
     A.epoch = H->epoch; A.kick = 1;
     A.vn = H->vn; A.un = H->un;
@@ -320,9 +325,8 @@ int step_once(sphb_handle *H) {
     SweepArgs A = sweep_args(H);
     A.Pstale = H->P; A.Pout = H->Pn;
     A.vh = H->vh; A.uh = H->uh;
-    A.hO = H->hn; A.rO = H->rhon; A.oO = H->omn;
-    A.F.hA = H->hn; A.F.rA = H->rhon; A.F.oA = H->omn; A.F.vA = H->vh; A.F.uA = H->uh;
-    A.F.hB = H->h; A.F.rB = H->rho; A.F.oB = H->oms; A.F.vB = H->vh; A.F.uB = H->uh;
+    A.F.vA = H->vh; A.F.uA = H->uh;
+    A.F.vB = H->vh; A.F.uB = H->uh;
     if (H->opt.order == SPHB_ORDER_JACOBI) {
         TRY(launch_first_sel<SEL_ALIVE>(H, A));
         phase_end(H, 4);
@@ -479,6 +483,8 @@ int sphb_create(const sphb_config *cfg, const sphb_options *opt_in, sphb_handle 
     rc |= dalloc(H, &H->cand, (size_t)H->cand_cap); rc |= dalloc(H, &H->gorder, (size_t)H->cand_cap);
     rc |= dalloc(H, &H->perm, (size_t)H->cap_alive); rc |= dalloc(H, &H->iota, (size_t)H->cap_alive);
     rc |= dalloc(H, &H->gkey, (size_t)H->cand_cap); rc |= dalloc(H, &H->d_ctl, 1);
+    rc |= dalloc(H, &H->wl0, (size_t)nblk(H->cap_alive, kTile) + 1); rc |= dalloc(H, &H->wl1, (size_t)nblk(H->cap_alive, kTile) + 1);
+    rc |= dalloc(H, &H->recA, T); rc |= dalloc(H, &H->recB, T);
     if (rc) return fail(SPHB_ERR_CUDA);
     CKC(cudaMallocHost((void **)&H->h_ctl, sizeof(Ctl)));
     memset(H->h_ctl, 0, sizeof(Ctl));
@@ -501,7 +507,8 @@ void sphb_destroy(sphb_handle *H) {
     void *ptrs[] = {H->x, H->v, H->u, H->a, H->du, H->h, H->rho, H->P, H->m, H->xalt, H->vh, H->uh, H->vn, H->un,
                     H->hn, H->rhon, H->omn, H->oms, H->Pn, H->tmp, H->gx, H->gv, H->gu, H->ga, H->gdu, H->gh,
                     H->grho, H->gP, H->gm, H->idx, H->idx_alt, H->slot_id, H->cnt, H->dirty, H->cand, H->gorder,
-                    H->perm, H->iota, H->gkey, H->d_ctl, H->cub_tmp, H->d_aos, H->d_newton, H->d_nbr};
+                    H->perm, H->iota, H->gkey, H->d_ctl, H->cub_tmp, H->d_aos, H->d_newton, H->d_nbr,
+                    H->wl0, H->wl1, H->recA, H->recB};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (H->h_ctl) cudaFreeHost(H->h_ctl);
     for (int i = 0; i <= SPHB_PHASES; i++) if (H->ev[i]) cudaEventDestroy(H->ev[i]);
@@ -667,9 +674,8 @@ int sphb_forces(sphb_handle *H) {
     A.kick = 0;
     A.Pstale = H->P; A.Pout = H->P;
     A.vh = H->v; A.uh = H->u;
-    A.hO = H->h; A.rO = H->rho; A.oO = H->omn;
-    A.F.hA = H->h; A.F.rA = H->rho; A.F.oA = H->omn; A.F.vA = H->v; A.F.uA = H->u;
-    A.F.hB = H->h; A.F.rB = H->rho; A.F.oB = H->omn; A.F.vB = H->v; A.F.uB = H->u;
+    A.F.vA = H->v; A.F.uA = H->u;
+    A.F.vB = H->v; A.F.uB = H->u;
     TRY(launch_first_sel<SEL_ALL_A>(H, A));
     return read_ctl(H);
 }
@@ -679,7 +685,7 @@ int sphb_omega(sphb_handle *H, double *omega, int cap) {
     CK(cudaSetDevice(H->device));
     TRY(ghosts_to_current(H));
     TRY(launch_begin(H, 0));
-    TRY(launch_density(H, 0, 0, 0, H->P));   // omega only: h, density stay as stored
+    TRY(launch_density(H, 0, 0, 0, H->P, true));   // omega only: h, density stay as stored
     TRY(read_ctl(H));
     const int n = H->na + H->h_ctl->GL + H->h_ctl->GR;
     if (n > cap) { H->err = "download buffer too small"; return SPHB_ERR_CAPACITY; }
@@ -864,6 +870,7 @@ int sphb_density_static(const double *d_x, const double *d_h, const double *d_rh
     DensityArgs A;
     A.x = d_x; A.m = nullptr; A.h = d_h; A.rho = d_rho; A.P = nullptr;
     A.hn = d_h_out; A.rhon = d_rho_out; A.omn = om_new; A.oms = om_stale; A.Pn = nullptr;
+    A.recA = nullptr; A.recB = nullptr;
     A.cnt = cnt; A.ctl = ctl; A.pad = 0; A.na = n;
     A.limit = limit; A.hfac = h_factor; A.m0 = mass;
     A.root_ghosts = 0; A.root_alive = 1; A.check_old = 0;

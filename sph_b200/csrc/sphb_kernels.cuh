@@ -35,7 +35,6 @@ constexpr double kSigma = 1.0 / 24.0;  // kernel.cpp:16
 constexpr unsigned kGhostBit = 0x80000000u;
 
 constexpr int kTile = 256;             // particles per CTA tile
-constexpr int kHalo = 128;             // x staged in shared memory on each side of a tile
 
 enum ErrCode {
     E_OK = 0, E_CAPACITY = 3, E_NEGATIVE_H = 4, E_LOW_DENSITY = 5, E_GHOST_ZERO_H = 6,
@@ -51,7 +50,7 @@ struct Ctl {
     int err_code, err_particle;    // first error wins
     unsigned long long hmax_bits;  // max over every h (old and new) in [lo,hi), as ordered bits
     unsigned long long fallbacks;  // bisection fallbacks taken
-    int nchanged[2];               // particles whose kicked (v,u) changed, by sweep parity
+    int nwork[2];                  // tiles in the work list of the sweep with even / odd stamp
     int sweeps_used;               // force sweeps the last step needed
     int pad_;
     unsigned long long force_pairs; // (i,j) pairs evaluated by the first force sweep (self included)
@@ -62,86 +61,107 @@ __device__ __forceinline__ void raise(Ctl *ctl, int code, int particle) {
 }
 
 // ------------------------------------------------------------------------------------
-// M5 quartic spline (kernel.cpp:14-64), branch-free: the three pieces are the clamped
-// powers of (5/2-q), (3/2-q), (1/2-q).  Returns w(q); dw receives dw/dq.
-__device__ __forceinline__ double m5(double q, double &dw) {
-    double t1 = fmax(2.5 - q, 0.0), t2 = fmax(1.5 - q, 0.0), t3 = fmax(0.5 - q, 0.0);
-    double s1 = t1 * t1, s2 = t2 * t2, s3 = t3 * t3;
-    double w = fma(10.0, s3 * s3, fma(-5.0, s2 * s2, s1 * s1));
-    double d = fma(-40.0, s3 * t3, fma(20.0, s2 * t2, -4.0 * (s1 * t1)));
-    dw = kSigma * d;
-    return kSigma * w;
-}
-__device__ __forceinline__ double m5_dw(double q) {
-    double t1 = fmax(2.5 - q, 0.0), t2 = fmax(1.5 - q, 0.0), t3 = fmax(0.5 - q, 0.0);
-    double d = fma(-40.0, (t3 * t3) * t3, fma(20.0, (t2 * t2) * t2, -4.0 * ((t1 * t1) * t1)));
-    return kSigma * d;
+// Arithmetic of the hot loops: the M5 quartic spline (kernel.cpp:14-64) in "r space".
+// With t_k = a_k h - r (a_k = 5/2, 3/2, 1/2) and T_k = max(t_k, 0) the pieces are T_k / h, so
+//     w(q)            = sigma / h^4 * [ T1^4 - 5 T2^4 + 10 T3^4 ]
+//     w(q) + q w'(q)  = sigma / h^4 * [ T1^3 (a1 h - 5 r) - 5 T2^3 (a2 h - 5 r) + 10 T3^3 (a3 h - 5 r) ]
+//     w'(q) / h^2     = sigma / h^5 * [ -4 T1^3 + 20 T2^3 - 40 T3^3 ]
+// — no division and no q per neighbour.  An FP64 max costs three instructions on sm_100a
+// (DSETP + 2 SEL); s = t + |t| = 2 max(t, 0) is ONE DADD and exact, and the powers of two it
+// brings in are folded into the coefficients (exactly).
+__device__ __forceinline__ double clamp2(double t) { return t + fabs(t); }   // 2 * max(t, 0)
+
+// [-4 T1^3 + 20 T2^3 - 40 T3^3] for smoothing length h at distance r >= 0
+__device__ __forceinline__ double dpoly(double r, double h) {
+    const double s1 = clamp2(fma(2.5, h, -r)), s2 = clamp2(fma(1.5, h, -r)), s3 = clamp2(fma(0.5, h, -r));
+    const double c1 = (s1 * s1) * s1, c2 = (s2 * s2) * s2, c3 = (s3 * s3) * s3;   // 8 T_k^3
+    return fma(-5.0, c3, fma(2.5, c2, -0.5 * c1));
 }
 
-// x window of a tile staged in shared memory, global fallback outside it.
-struct XWin {
-    const double *__restrict__ g;
-    const double *sm;
-    int base, n;
-    __device__ __forceinline__ double operator()(int j) const {
-        int k = j - base;
-        return ((unsigned)k < (unsigned)n) ? sm[k] : __ldg(g + j);
-    }
+// What the density pass leaves per particle for the force pass: everything a pair needs from
+// its neighbour without a division.
+struct __align__(32) Rec {
+    double h;     // smoothing length
+    double c5;    // sigma / h^5
+    double rho;   // density
+    double kap;   // 1 / (rho * omega):  P / (rho^2 omega) = (gamma - 1) u kap (adiabatic), kap (isothermal)
 };
 
+constexpr int kDHalo = 64;    // density pass: x staged on each side of a tile
+constexpr int kFHalo = 32;    // force pass: neighbour state staged on each side of a tile
+
 // ------------------------------------------------------------------------------------
-// One evaluation of the two density-pass sums at trial smoothing length h:
-//   sw = sum_j w(q_j)                      (calc_density, smoothing_length.cpp:80-91,
-//                                           without the common factor m_i / h)
-//   sd = sum_j m_j (w(q_j) + q_j w'(q_j))  (calc_density_dh, :53-62, without -1/h^2)
-//   cnt = #{ j : |x_i - x_j| / h < 2.5 }   with the reference's IEEE division
-// over the sorted window, self included.  The scan stops at the first q >= 2.5: the
-// array is x-sorted, so every farther particle is outside the support as well.
+// One evaluation of the two density-pass sums at trial smoothing length h over the sorted
+// window, self included:
+//   Sw = sum_j [T1^4 - 5 T2^4 + 10 T3^4]           so that  sum_j w(q_j)              = sigma/h^4 Sw
+//   Sg = sum_j m_j [T1^3 (a1 h - 5 r) - ...]        so that  sum_j m_j (w + q w')(q_j) = sigma/h^4 Sg
+//   cnt = #{ j : |x_i - x_j| / h < 2.5 }            with the reference's IEEE division (kernel.cpp:31)
+// sx is the staged window, sx[k] = x[wbase + k] for 0 <= k < wn, with +-INF sentinels at
+// sx[-1] and sx[wn]; a scan that runs off the staged part goes on in global memory.  The scan
+// stops at the first particle outside the support: the array is x-sorted, so every farther
+// one is outside as well.
 template <bool UM>
-__device__ __forceinline__ void density_sums(const XWin &X, const double *__restrict__ m, double m0,
-                                             int s, int lo, int hi, double xi, double h,
-                                             double &sw, double &sd, int &cnt) {
-    const double ih = 1.0 / h;
-    double dw0;
-    double w0 = m5(0.0, dw0);
-    double mi = UM ? m0 : __ldg(m + s);
-    sw = w0;
-    sd = mi * w0;
-    cnt = 1;
-    const double q_in = 2.5 * (1.0 - 0x1p-48), q_out = 2.5 * (1.0 + 0x1p-48);
+__device__ __forceinline__ void density_sums(const double *sx, int wbase, int wn, const double *__restrict__ gx,
+                                             const double *__restrict__ m, int s, int lo, int hi, double xi,
+                                             double h, double &Sw, double &Sg, int &cnt) {
+    const double a1 = 2.5 * h, a2 = 1.5 * h, a3 = 0.5 * h;
+    const double r_in = a1 * (1.0 - 0x1p-48);     // below: certainly inside; from here on decide exactly
+    double sw16 = 0.0, sg8 = 0.0;                 // sums over j != i in units of s_k = 2 T_k
+    int c = 1;
 #pragma unroll 1
     for (int side = 0; side < 2; side++) {
-        int j = side ? s + 1 : s - 1;
         const int step = side ? 1 : -1;
+        int k = s - wbase + step;
+        bool staged = true;
 #pragma unroll 1
-        for (; side ? (j < hi) : (j >= lo); j += step) {
-            double r = side ? (X(j) - xi) : (xi - X(j));
-            double q = r * ih;
-            if (q >= q_out) break;
-            if (q > q_in) {                 // within rounding of the support edge: decide the
-                if (r / h < kRadius) cnt++; // count exactly; the kernel value there is ~0
-                else break;
-                continue;
+        while (true) {
+            double xj;
+            if (staged) {
+                xj = sx[k];
+            } else {
+                const int j = wbase + k;
+                if (j < lo || j >= hi) break;
+                xj = __ldg(gx + j);
             }
-            cnt++;
-            double dw;
-            double w = m5(q, dw);
-            double mj = UM ? m0 : __ldg(m + j);
-            sw += w;
-            sd = fma(mj, fma(q, dw, w), sd);
+            const double r = side ? (xj - xi) : (xi - xj);
+            if (!(r < r_in)) {
+                if (staged && (k < 0 || k >= wn)) {       // sentinel: end of the staged part ...
+                    const int j = wbase + k;
+                    if (j < lo || j >= hi) break;         // ... which is also the end of the array
+                    staged = false;                       // rare: more than kDHalo neighbours on one side
+                    continue;
+                }
+                if (r / h < kRadius) { c++; k += step; continue; }   // on the edge: counts, contributes < 1e-57 h^4
+                break;
+            }
+            c++;
+            const double s1 = clamp2(a1 - r), s2 = clamp2(a2 - r), s3 = clamp2(a3 - r);
+            const double c1 = (s1 * s1) * s1, c2 = -5.0 * ((s2 * s2) * s2), c3 = 10.0 * ((s3 * s3) * s3);
+            const double r5 = 5.0 * r;
+            sw16 = fma(c3, s3, fma(c2, s2, fma(c1, s1, sw16)));
+            const double g = fma(c3, a3 - r5, fma(c2, a2 - r5, c1 * (a1 - r5)));
+            if (UM) sg8 += g; else sg8 = fma(__ldg(m + wbase + k), g, sg8);
+            k += step;
         }
     }
+    const double h2 = h * h;
+    const double self = 14.375 * (h2 * h2);       // r = 0: (5/2)^4 - 5 (3/2)^4 + 10 (1/2)^4, times h^4
+    Sw = fma(0.0625, sw16, self);
+    Sg = UM ? fma(0.125, sg8, self) : fma(0.125, sg8, self * __ldg(m + s));
+    cnt = c;
 }
 
 struct DensityArgs {
     const double *x, *m, *h, *rho, *P;
-    double *hn, *rhon, *omn, *oms, *Pn;
+    double *hn, *rhon, *Pn;
+    double *omn, *oms;   // omega for the new / the old (h, rho) at the new positions; may be null
+    Rec *recA, *recB;    // force-pass records of the new / the old state; may be null
     int *cnt;            // (newton_iters << 24) | neighbour count
     Ctl *ctl;
     int pad, na;
     double limit, hfac, m0;
     int root_ghosts;     // 1: ghosts are root-found too (t = 0, setup.cpp:218-220)
-    int root_alive;      // 0: omega-only pass (keeps h, rho; used by sphb_forces)
+    int root_alive;      // 0: omega-only pass (keeps h, rho; used by sphb_forces / sphb_omega)
     int check_old;       // 1: the old (h, rho) state is also seen by force sums (step path)
 };
 
@@ -152,38 +172,49 @@ struct DensityArgs {
 // The last Newton evaluation is at the returned h, so its sums ARE the final density
 // (calculators.cpp:45) and omega_new; the first evaluation is at the old h, so its
 // derivative sum gives omega_stale = calc_omega(old h, old rho) at the new positions.
+// With f(h) = m_i sigma Sw / h^5 - m_i hf / h and f'(h) = -sigma Sg / h^6 + m_i hf / h^2.
 template <bool VARH, bool UM>
 __global__ void __launch_bounds__(kTile) k_density(DensityArgs A) {
-    __shared__ double sx[kTile + 2 * kHalo];
+    __shared__ double sxs[kTile + 2 * kDHalo + 2];
+    double *sx = sxs + 1;
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
     const int t0 = blockIdx.x * kTile;          // grid covers [0, pad + na + pad)
     if (t0 >= hi || t0 + kTile <= lo) return;
-    const int wbase = max(t0 - kHalo, lo);
-    const int wend = min(t0 + kTile + kHalo, hi);
-    for (int k = threadIdx.x; k < wend - wbase; k += kTile) sx[k] = A.x[wbase + k];
+    const int wbase = max(t0 - kDHalo, lo);
+    const int wn = min(t0 + kTile + kDHalo, hi) - wbase;
+    for (int k = threadIdx.x; k < wn; k += kTile) sx[k] = A.x[wbase + k];
+    if (threadIdx.x == 0) { sx[-1] = -INFINITY; sx[wn] = INFINITY; }
     __syncthreads();
-    XWin X{A.x, sx, wbase, wend - wbase};
 
     const int s = t0 + threadIdx.x;
     double hloc = 0.0;
     if (s >= lo && s < hi) {
         const bool is_pad = (s < A.pad) || (s >= A.pad + A.na);
         const bool do_root = VARH && (is_pad ? A.root_ghosts : A.root_alive);
-        const double xi = X(s);
+        const double xi = sx[s - wbase];
         const double mi = UM ? A.m0 : A.m[s];
+        const double msig = UM ? kSigma : 1.0;   // with uniform masses Sg lacks the factor m_j = m0
         const double hold = A.h[s], rhoold = A.rho[s];
         const int npart = A.na + ctl->GL + ctl->GR;
         double hnew = hold, rhonew = rhoold, om_new = 1.0, om_stale = 1.0;
         int iters = 0, cnt = 0;
-        double sw, sd;
+        double Sw, Sg;
+#define SPHB_EVAL(H_, F_, DF_, DSUM_)                                                           \
+    {                                                                                           \
+        density_sums<UM>(sx, wbase, wn, A.x, A.m, s, lo, hi, xi, (H_), Sw, Sg, cnt);            \
+        const double ih_ = 1.0 / (H_), ih2_ = ih_ * ih_, ih4_ = ih2_ * ih2_;                    \
+        const double rho_ = mi * (kSigma * (Sw * (ih4_ * ih_)));                                \
+        F_ = rho_ - mi * A.hfac * ih_;                                                          \
+        DSUM_ = UM ? -(mi * (kSigma * (Sg * (ih4_ * ih2_)))) : -(kSigma * (Sg * (ih4_ * ih2_))); \
+        DF_ = DSUM_ + mi * A.hfac * ih2_;                                                       \
+        rho_cur = rho_;                                                                         \
+    }
+        (void)msig;
         if (VARH) {
-            double x0 = hold > kEps ? hold : A.hfac * (2 * A.limit / (npart - 1));
-            density_sums<UM>(X, A.m, A.m0, s, lo, hi, xi, x0, sw, sd, cnt);
-            double ih = 1.0 / x0;
-            double f = mi * (sw * ih) - mi * A.hfac * ih;
-            double dsum = -(sd * ih * ih);                    // sum_j m_j dW/dh
-            double df = dsum + mi * A.hfac * ih * ih;
+            const double x0 = hold > kEps ? hold : A.hfac * (2 * A.limit / (npart - 1));
+            double f, df, dsum, rho_cur;
+            SPHB_EVAL(x0, f, df, dsum);
             om_stale = 1.0 - dsum * (-hold / rhoold);
             if (do_root) {
                 double xcur = x0;
@@ -192,26 +223,20 @@ __global__ void __launch_bounds__(kTile) k_density(DensityArgs A) {
                 while (cont && iters < kMaxIterNR) {
                     iters++;
                     if (df == 0.0) { raise(ctl, E_ZERO_DERIVATIVE, s); break; }
-                    double xn = xcur - f / df;
-                    density_sums<UM>(X, A.m, A.m0, s, lo, hi, xi, xn, sw, sd, cnt);
-                    ih = 1.0 / xn;
-                    f = mi * (sw * ih) - mi * A.hfac * ih;
-                    dsum = -(sd * ih * ih);
-                    df = dsum + mi * A.hfac * ih * ih;
+                    const double xn = xcur - f / df;
+                    SPHB_EVAL(xn, f, df, dsum);
                     if (!isfinite(f) || !isfinite(df)) { raise(ctl, E_NOT_FINITE, s); break; }
-                    double xprev = xcur;
+                    const double xprev = xcur;
                     xcur = xn;
                     cont = !(fabs(xcur - xprev) < kHEps * fabs(xcur) || xcur == xprev);
                 }
                 if (cont && ctl->err_code == 0) {
                     // bisection fallback on [1e-8, 2 limit], gsl_root_test_interval rel 1e-4
                     atomicAdd(&ctl->fallbacks, 1ull);
-                    double xl = kEps, xh = 2 * A.limit, fl, fh;
-                    int c2;
-                    density_sums<UM>(X, A.m, A.m0, s, lo, hi, xi, xl, sw, sd, c2);
-                    fl = mi * (sw / xl) - mi * A.hfac / xl;
-                    density_sums<UM>(X, A.m, A.m0, s, lo, hi, xi, xh, sw, sd, c2);
-                    fh = mi * (sw / xh) - mi * A.hfac / xh;
+                    double xl = kEps, xh = 2 * A.limit, fl, fh, dfx, dsx;
+                    int c2 = cnt;
+                    SPHB_EVAL(xl, fl, dfx, dsx);
+                    SPHB_EVAL(xh, fh, dfx, dsx);
                     double root = 0.5 * (xl + xh);
                     if (!isfinite(fl) || !isfinite(fh)) raise(ctl, E_NOT_FINITE, s);
                     else if ((fl < 0.0 && fh < 0.0) || (fl > 0.0 && fh > 0.0)) raise(ctl, E_NO_BRACKET, s);
@@ -224,9 +249,9 @@ __global__ void __launch_bounds__(kTile) k_density(DensityArgs A) {
                             if (fl == 0.0) { root = xl; xh = xl; }
                             else if (fh == 0.0) { root = xh; xl = xh; }
                             else {
-                                double mid = (xl + xh) / 2.0;
-                                density_sums<UM>(X, A.m, A.m0, s, lo, hi, xi, mid, sw, sd, c2);
-                                double fm = mi * (sw / mid) - mi * A.hfac / mid;
+                                const double mid = (xl + xh) / 2.0;
+                                double fm;
+                                SPHB_EVAL(mid, fm, dfx, dsx);
                                 if (!isfinite(fm)) { raise(ctl, E_NOT_FINITE, s); break; }
                                 if (fm == 0.0) { root = mid; xl = mid; xh = mid; }
                                 else if ((fl > 0.0 && fm < 0.0) || (fl < 0.0 && fm > 0.0)) {
@@ -240,26 +265,42 @@ __global__ void __launch_bounds__(kTile) k_density(DensityArgs A) {
                             go = !(fabs(xh - xl) < kHEps * smallest);
                         }
                     }
+                    (void)c2;
                     xcur = root;
-                    density_sums<UM>(X, A.m, A.m0, s, lo, hi, xi, xcur, sw, sd, cnt);
-                    ih = 1.0 / xcur;
-                    dsum = -(sd * ih * ih);
+                    SPHB_EVAL(xcur, f, df, dsum);
                 }
                 if (xcur < 0) raise(ctl, E_NEGATIVE_H, s);
                 hnew = xcur;
-                rhonew = mi * (sw * ih);
+                rhonew = rho_cur;
                 om_new = 1.0 - dsum * (-hnew / rhonew);
             } else {
                 om_new = om_stale;   // particle keeps its stored h, rho: omega for those
             }
         } else {
-            density_sums<UM>(X, A.m, A.m0, s, lo, hi, xi, hold, sw, sd, cnt);
-            if (is_pad ? A.root_ghosts : A.root_alive) rhonew = mi * (sw / hold);
+            double f, df, dsum, rho_cur;
+            SPHB_EVAL(hold, f, df, dsum);
+            (void)f; (void)df; (void)dsum;
+            if (is_pad ? A.root_ghosts : A.root_alive) rhonew = rho_cur;
         }
+#undef SPHB_EVAL
         A.hn[s] = hnew;
         A.rhon[s] = rhonew;
-        A.omn[s] = om_new;
-        A.oms[s] = om_stale;
+        if (A.omn) { A.omn[s] = om_new; A.oms[s] = om_stale; }
+        if (A.recA) {
+            // c5 = sigma / h^5 and kap = 1 / (rho omega): the only divisions the force pass would need
+            const double ihn = 1.0 / hnew, ihn2 = ihn * ihn;
+            Rec ra;
+            ra.h = hnew; ra.c5 = kSigma * ((ihn2 * ihn2) * ihn); ra.rho = rhonew; ra.kap = 1.0 / (rhonew * om_new);
+            A.recA[s] = ra;
+            Rec rb = ra;
+            if (VARH && A.check_old) {
+                const double iho = 1.0 / hold, iho2 = iho * iho;
+                rb.h = hold; rb.c5 = kSigma * ((iho2 * iho2) * iho); rb.rho = rhoold; rb.kap = 1.0 / (rhoold * om_stale);
+            } else if (A.check_old) {
+                rb.rho = rhoold; rb.kap = 1.0 / rhoold;      // fixed h: omega = 1, h unchanged
+            }
+            A.recB[s] = rb;
+        }
         if (A.root_alive || A.root_ghosts) A.cnt[s] = (iters << 24) | (cnt & 0xffffff);
         if (is_pad && A.Pn != A.P) A.Pn[s] = A.P[s];
         // ensure_nonzero_density (calculators.cpp:174-186) guards every particle a force sum
@@ -289,94 +330,12 @@ struct ForceArrays {
     const double *x;
     const unsigned *idx;
     const double *m;
-    const double *hA, *rA, *oA, *vA, *uA;
-    const double *hB, *rB, *oB, *vB, *uB;
+    const Rec *recA, *recB;
+    const double *vA, *uA;     // current iterate of the fully kicked v, u (read with .cg: other CTAs update it)
+    const double *vB, *uB;     // half-kicked base state
 };
 
 enum { SEL_INDEX = 0, SEL_ALIVE = 1, SEL_ALL_A = 2 };
-
-template <bool VOL>
-__device__ __forceinline__ double ld(const double *p) {
-    return VOL ? __ldcg(p) : __ldg(p);
-}
-
-template <int SEL, bool ADIA, bool UM, bool VOL>
-__device__ __forceinline__ void force_eval(const ForceArrays &F, double m0, int s, int lo, int hi,
-                                           double Hb, double xi, unsigned idxi, double hi_, double rhoi,
-                                           double omi, double vi, double ui, double Pstale,
-                                           double &acc, double &dudt, double &Pi_out, int &jmin, int &jmax, int &npairs) {
-    const double Pi = ADIA ? ((kGamma - 1) * ui) * rhoi : rhoi;
-    const double c_ac = ADIA ? sqrt(kGamma * Pstale / rhoi) : 1.0;   // stale stored pressure (F7)
-    const double c_ec = ADIA ? sqrt(kGamma * Pi / rhoi) : 1.0;       // fresh pressure
-    const double PrRho_i = Pi / (rhoi * rhoi) / omi;
-    const double ihi = 1.0 / hi_;
-    const double ihi2 = ihi * ihi;
-    const double reach = kRadius * Hb;
-    double a_sum = 0.0, e_sum = 0.0;
-    jmin = s; jmax = s;
-    Pi_out = Pi;
-    npairs = 1;   // self: its energy term is evaluated by the reference too (and is exactly 0)
-#pragma unroll 1
-    for (int side = 0; side < 2; side++) {
-        int j = side ? s + 1 : s - 1;
-        const int step = side ? 1 : -1;
-#pragma unroll 1
-        for (; side ? (j < hi) : (j >= lo); j += step) {
-            const double xj = __ldg(F.x + j);
-            const double r = xi - xj;
-            const double ar = fabs(r);
-            if (ar >= reach) break;
-            if (side) jmax = j; else jmin = j;
-            const unsigned idxj = __ldg(F.idx + j);
-            bool useA;
-            if (SEL == SEL_INDEX) useA = idxj < idxi;
-            else if (SEL == SEL_ALIVE) useA = !(idxj & kGhostBit);
-            else useA = true;
-            const double hj = useA ? ld<false>(F.hA + j) : __ldg(F.hB + j);
-            if (ar >= kRadius * fmax(hi_, hj)) continue;   // all three gradients vanish
-            npairs++;
-            const double rhoj = useA ? __ldg(F.rA + j) : __ldg(F.rB + j);
-            const double omj = useA ? __ldg(F.oA + j) : __ldg(F.oB + j);
-            const double vj = useA ? ld<VOL>(F.vA + j) : __ldg(F.vB + j);
-            const double uj = useA ? ld<VOL>(F.uA + j) : __ldg(F.uB + j);
-            const double mj = UM ? m0 : __ldg(F.m + j);
-            // grad_W (calculators.cpp:17-27) with h_i, h_j and the mean h; r == 0 counts as "<= 0"
-            const double sg = (r > 0) ? 1.0 : -1.0;
-            const double hij = (hi_ + hj) / 2;
-            const double v_ij = vi - vj;
-            const double dot = v_ij * r;
-            const double rho_sum = rhoi + rhoj;
-            const double D = fma(r, r, 0.01 * (hij * hij));
-            // one reciprocal serves 1/h_ij, 1/D and 1/rho_sum
-            const double R = 1.0 / (hij * D * rho_sum);
-            const double ihij = R * (D * rho_sum);
-            const double iD = R * (hij * rho_sum);
-            const double irs = R * (hij * D);
-            const double ihj = 1.0 / hj;
-            const double gWi = sg * (m5_dw(ar * ihi) * ihi2);
-            const double gWj = sg * (m5_dw(ar * ihj) * (ihj * ihj));
-            const double gWij = sg * (m5_dw(ar * ihij) * (ihij * ihij));
-            const double Pj = ADIA ? ((kGamma - 1) * uj) * rhoj : rhoj;
-            const double PrRho_j = Pj / (rhoj * rhoj) / omj;
-            // artificial viscosity (calculators.cpp:148-172): alpha = 1, beta = 2
-            double visc_ac = 0.0, visc_ec = 0.0;
-            if (!(dot > 0)) {
-                const double mu = (hij * dot) * iD;
-                const double two_mu2 = 2.0 * (mu * mu);
-                const double irho = 2.0 * irs;             // 1 / ((rho_i + rho_j) / 2)
-                visc_ac = fma(-c_ac, mu, two_mu2) * irho;
-                visc_ec = fma(-c_ec, mu, two_mu2) * irho;
-            }
-            if (idxj != idxi)
-                a_sum -= mj * fma(gWij, visc_ac, fma(gWj, PrRho_j, gWi * PrRho_i));
-            const double mv = mj * v_ij;
-            e_sum = fma(PrRho_i * mv, gWij, e_sum);
-            e_sum = fma((0.5 * mv) * visc_ec, gWij, e_sum);
-        }
-    }
-    acc = a_sum;
-    dudt = e_sum;
-}
 
 struct SweepArgs {
     ForceArrays F;
@@ -385,8 +344,8 @@ struct SweepArgs {
     double *a, *du;         // outputs
     double *vn, *un;        // fully-kicked outputs (iterate)
     const double *vh, *uh;  // half-kicked base state of i itself
-    const double *hO, *rO, *oO;   // own h, rho, omega of i
     int *dirty;             // per-tile stamp: epoch of the last sweep that changed something in range
+    int *wl[2];             // work lists of tiles for the sweeps of even / odd epoch
     Ctl *ctl;
     int pad, na;
     double m0, half_dt;
@@ -394,49 +353,216 @@ struct SweepArgs {
     int kick;               // 0: t = 0 semantics (no kick, calculators only)
 };
 
-__device__ __forceinline__ void mark_dirty(int *dirty, int pad, int na, int jmin, int jmax, int epoch) {
-    int ntiles = (na + kTile - 1) / kTile;
-    int t0 = max((jmin - pad) / kTile, 0), t1 = min((jmax - pad) / kTile, ntiles - 1);
-    if (jmin < pad) t0 = 0;
-    for (int t = t0; t <= t1; t++) dirty[t] = epoch;
+// per-thread invariants of one force evaluation
+template <bool ADIA>
+struct Own {
+    double x, h, rho, v, PrRho, Ci, c_ac, c_ec, P;
+    unsigned idx;
+    __device__ __forceinline__ void set(double xi, unsigned idxi, const Rec &r, double vi, double ui, double Pstale) {
+        x = xi; idx = idxi; h = r.h; rho = r.rho; v = vi;
+        P = ADIA ? ((kGamma - 1) * ui) * r.rho : r.rho;                 // calculators.cpp:131-137
+        c_ac = ADIA ? sqrt(kGamma * Pstale / r.rho) : 1.0;              // stale stored pressure
+        c_ec = ADIA ? sqrt(kGamma * P / r.rho) : 1.0;                   // fresh pressure
+        PrRho = ADIA ? ((kGamma - 1) * ui) * r.kap : r.kap;             // P_i / (rho_i^2 omega_i)
+        Ci = PrRho * r.c5;
+    }
+};
+
+// One (i, j) pair; ar = |x_i - x_j| >= 0 and the sign of the gradient is applied by the
+// caller per side.  accA gathers m_j [gradW(h_i) P_i/(rho_i^2 om_i) + gradW(h_j) P_j/(rho_j^2 om_j)
+// + gradW(hbar) Pi_ij(c_ac)], accE gathers m_j v_ij gradW(hbar) [P_i/(rho_i^2 om_i) + Pi_ij(c_ec)/2],
+// both without the sign.  dir = +1 for a left neighbour (x_i - x_j = +ar), -1 for a right one.
+template <bool ADIA, bool UM>
+__device__ __forceinline__ bool pair_terms(const Own<ADIA> &o, double ar, double dir, const Rec &rj, double vj,
+                                           double uj, double mj, double &accA, double &accE) {
+    const double hj = rj.h;
+    if (ar >= kRadius * fmax(o.h, hj)) return false;     // all three gradients vanish
+    const double hb = 0.5 * (o.h + hj);
+    const double rs = o.rho + rj.rho;
+    const double D = fma(ar, ar, 0.01 * (hb * hb));
+    // one reciprocal serves 1/hbar, 1/D and 1/(rho_i + rho_j)
+    const double DP = D * rs;
+    const double R = 1.0 / (hb * DP);
+    const double ihb = R * DP;
+    const double t = R * hb;              // 1 / (D rs)
+    const double iD = t * rs;
+    const double irs = t * D;
+    const double ihb2 = ihb * ihb;
+    const double gb = dpoly(ar, hb) * (kSigma * ((ihb2 * ihb2) * ihb));     // |gradW(hbar)| with its own sign of w'
+    const double PrRho_j = ADIA ? ((kGamma - 1) * uj) * rj.kap : rj.kap;
+    const double gi = dpoly(ar, o.h) * o.Ci;
+    const double gj = dpoly(ar, hj) * (rj.c5 * PrRho_j);
+    const double v_ij = o.v - vj;
+    const double dot = v_ij * (dir * ar);
+    // artificial viscosity (calculators.cpp:148-172): alpha = 1, beta = 2, eta^2 = 0.01 hbar^2
+    double visc_ac = 0.0, visc_ec = 0.0;
+    if (!(dot > 0)) {
+        const double mu = (hb * dot) * iD;
+        const double two_mu2 = 2.0 * (mu * mu);
+        const double irho = 2.0 * irs;               // 1 / ((rho_i + rho_j) / 2)
+        visc_ac = fma(-o.c_ac, mu, two_mu2) * irho;
+        visc_ec = fma(-o.c_ec, mu, two_mu2) * irho;
+    }
+    const double ta = fma(gb, visc_ac, gi + gj);
+    const double te = (v_ij * gb) * fma(0.5, visc_ec, o.PrRho);
+    if (UM) { accA += ta; accE += te; }
+    else { accA = fma(mj, ta, accA); accE = fma(mj, te, accE); }
+    return true;
+}
+
+// Shared-memory image of a tile and its surroundings for the force pass.
+struct ForceSmem {
+    double x[kTile + 2 * kFHalo + 2];
+    Rec rA[kTile + 2 * kFHalo];
+    Rec rB[kTile + 2 * kFHalo];
+    double vA[kTile + 2 * kFHalo], uA[kTile + 2 * kFHalo];
+    double vB[kTile + 2 * kFHalo], uB[kTile + 2 * kFHalo];
+    unsigned idx[kTile + 2 * kFHalo];
+};
+
+template <bool VOL>
+__device__ __forceinline__ double ldv(const double *p) { return VOL ? __ldcg(p) : __ldg(p); }
+
+// Evaluate one tile: stage, compute a, du/dt (and the kick), store.  Returns through
+// `changed_any` whether any particle's kicked (v, u) differs from what was stored before.
+// FIRST: sweep 1 of a step (vA == vB: everybody is seen half-kicked, outputs always stored).
+template <int SEL, bool ADIA, bool UM, bool FIRST>
+__device__ __forceinline__ void force_tile(const SweepArgs &A, ForceSmem &S, int tile, int lo, int hi, double Hb,
+                                           int epoch, bool &changed_any, int &npairs_out) {
+    const int t0 = A.pad + tile * kTile;
+    const int tend = min(t0 + kTile, A.pad + A.na);
+    const int wbase = max(t0 - kFHalo, lo);
+    const int wn = min(t0 + kTile + kFHalo, hi) - wbase;
+    double *sx = S.x + 1;
+    __syncthreads();                                   // previous tile's readers are done
+    for (int k = threadIdx.x; k < wn; k += kTile) {
+        const int j = wbase + k;
+        sx[k] = A.F.x[j];
+        S.idx[k] = A.F.idx[j];
+        S.rB[k] = A.F.recB[j];
+        S.vB[k] = __ldg(A.F.vB + j);
+        S.uB[k] = __ldg(A.F.uB + j);
+        S.rA[k] = A.F.recA[j];
+        if (!FIRST) { S.vA[k] = ldv<true>(A.F.vA + j); S.uA[k] = ldv<true>(A.F.uA + j); }
+    }
+    if (threadIdx.x == 0) { sx[-1] = -INFINITY; sx[wn] = INFINITY; }
+    __syncthreads();
+
+    const int s = t0 + threadIdx.x;
+    bool changed = false;
+    int npairs = 0;
+    if (s < tend) {
+        const int ks = s - wbase;
+        Own<ADIA> o;
+        const double vi = A.vh[s], ui = A.uh[s];
+        o.set(sx[ks], S.idx[ks], S.rA[ks], vi, ui, A.Pstale[s]);
+        const double reach = kRadius * Hb;
+        double a_sum = 0.0, e_sum = 0.0;
+        int jmin = s, jmax = s;
+        npairs = 1;   // self: its energy term is evaluated by the reference too (and is exactly 0)
+#pragma unroll 1
+        for (int side = 0; side < 2; side++) {
+            const int step = side ? 1 : -1;
+            const double dir = side ? -1.0 : 1.0;
+            double accA = 0.0, accE = 0.0;
+            int k = ks + step;
+#pragma unroll 1
+            while (true) {                              // staged part
+                const double ar = side ? (sx[k] - o.x) : (o.x - sx[k]);
+                if (!(ar < reach)) break;               // also the +-INF sentinels
+                const unsigned idxj = S.idx[k];
+                bool useA;
+                if (SEL == SEL_INDEX) useA = idxj < o.idx;
+                else if (SEL == SEL_ALIVE) useA = !(idxj & kGhostBit);
+                else useA = true;
+                const Rec rj = useA ? S.rA[k] : S.rB[k];
+                const double vj = (useA && !FIRST) ? S.vA[k] : S.vB[k];
+                const double uj = (useA && !FIRST) ? S.uA[k] : S.uB[k];
+                const double mj = UM ? 0.0 : __ldg(A.F.m + wbase + k);
+                if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
+                k += step;
+            }
+            int j = wbase + k;                          // first particle not handled above
+            if ((k < 0 || k >= wn) && j >= lo && j < hi) {
+                // rare: the support reaches beyond the staged halo — continue in global memory
+#pragma unroll 1
+                for (; j >= lo && j < hi; j += step) {
+                    const double xj = __ldg(A.F.x + j);
+                    const double ar = side ? (xj - o.x) : (o.x - xj);
+                    if (!(ar < reach)) break;
+                    const unsigned idxj = __ldg(A.F.idx + j);
+                    bool useA;
+                    if (SEL == SEL_INDEX) useA = idxj < o.idx;
+                    else if (SEL == SEL_ALIVE) useA = !(idxj & kGhostBit);
+                    else useA = true;
+                    const Rec rj = useA ? A.F.recA[j] : A.F.recB[j];
+                    const double vj = (useA && !FIRST) ? ldv<true>(A.F.vA + j) : __ldg(A.F.vB + j);
+                    const double uj = (useA && !FIRST) ? ldv<true>(A.F.uA + j) : __ldg(A.F.uB + j);
+                    const double mj = UM ? 0.0 : __ldg(A.F.m + j);
+                    if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
+                }
+                j -= step;
+            } else {
+                j -= step;
+            }
+            if (side) jmax = max(j, s); else jmin = min(j, s);
+            // gradW carries sign(x_i - x_j) (calculators.cpp:17-27): + for left neighbours, - for right
+            a_sum = side ? (a_sum + accA) : (a_sum - accA);
+            e_sum = side ? (e_sum - accE) : (e_sum + accE);
+        }
+        if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
+        if (!A.kick) {
+            A.a[s] = a_sum;
+            A.du[s] = e_sum;
+            A.Pout[s] = o.P;
+        } else {
+            // second half-kick, sph_simulation.cpp:105-106, operation by operation
+            const double vf = __dadd_rn(vi, __dmul_rn(a_sum, A.half_dt));
+            const double uf = __dadd_rn(ui, __dmul_rn(e_sum, A.half_dt));
+            if (FIRST) {
+                A.a[s] = a_sum; A.du[s] = e_sum; A.Pout[s] = o.P;
+                A.vn[s] = vf; A.un[s] = uf;
+                // later-index neighbours used (vh, uh) as their guess for this particle
+                changed = (__double_as_longlong(vf) != __double_as_longlong(vi)) ||
+                          (__double_as_longlong(uf) != __double_as_longlong(ui));
+            } else {
+                const double vo = __ldcg(A.vn + s), uo = __ldcg(A.un + s);
+                changed = (__double_as_longlong(vf) != __double_as_longlong(vo)) ||
+                          (__double_as_longlong(uf) != __double_as_longlong(uo));
+                if (changed) {
+                    A.a[s] = a_sum; A.du[s] = e_sum;
+                    __stcg(A.vn + s, vf); __stcg(A.un + s, uf);
+                }
+            }
+            if (changed && SEL == SEL_INDEX) {
+                // every tile holding a particle within reach must be looked at again next sweep
+                const int ntiles = (A.na + kTile - 1) / kTile;
+                int ta = max((jmin - A.pad) / kTile, 0), tb = min((jmax - A.pad) / kTile, ntiles - 1);
+                if (jmin < A.pad) ta = 0;
+                for (int t = ta; t <= tb; t++) {
+                    if (atomicMax(A.dirty + t, epoch) < epoch) {
+                        const int slot = atomicAdd(&A.ctl->nwork[(epoch + 1) & 1], 1);
+                        A.wl[(epoch + 1) & 1][slot] = t;
+                    }
+                }
+            }
+        }
+    }
+    changed_any = changed;
+    npairs_out = npairs;
 }
 
 // First force sweep of a step over every alive particle (also the only one for the
 // jacobi order and for the kick-less t = 0 pass).
 template <int SEL, bool ADIA, bool UM>
 __global__ void __launch_bounds__(kTile) k_force_first(SweepArgs A) {
+    __shared__ ForceSmem S;
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
-    const int s = A.pad + blockIdx.x * kTile + threadIdx.x;
-    bool changed = false;
-    int npairs = 0;
-    if (s < A.pad + A.na) {
-        const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
-        double acc, dudt, Pi;
-        int jmin, jmax;
-        const double vi = A.vh[s], ui = A.uh[s];
-        force_eval<SEL, ADIA, UM, false>(A.F, A.m0, s, lo, hi, Hb, A.F.x[s], A.F.idx[s], A.hO[s], A.rO[s],
-                                         A.oO[s], vi, ui, A.Pstale[s], acc, dudt, Pi, jmin, jmax, npairs);
-        A.a[s] = acc;
-        A.du[s] = dudt;
-        A.Pout[s] = Pi;
-        if (A.kick) {
-            // second half-kick, sph_simulation.cpp:105-106, operation by operation
-            const double vf = __dadd_rn(vi, __dmul_rn(acc, A.half_dt));
-            const double uf = __dadd_rn(ui, __dmul_rn(dudt, A.half_dt));
-            A.vn[s] = vf;
-            A.un[s] = uf;
-            if (SEL == SEL_INDEX) {
-                // later-index neighbours used (vh, uh) as a guess for this particle
-                changed = (__double_as_longlong(vf) != __double_as_longlong(vi)) ||
-                          (__double_as_longlong(uf) != __double_as_longlong(ui));
-                if (changed) mark_dirty(A.dirty, A.pad, A.na, jmin, jmax, A.epoch);
-            }
-        }
-    }
-    if (SEL == SEL_INDEX && A.kick) {
-        if (__syncthreads_or(changed) && threadIdx.x == 0) atomicAdd(&ctl->nchanged[A.epoch & 1], 1);
-    }
+    const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
+    bool changed;
+    int npairs;
+    force_tile<SEL, ADIA, UM, true>(A, S, blockIdx.x, lo, hi, Hb, A.epoch, changed, npairs);
     // pair statistics for the roofline accounting (one atomic per warp)
     for (int o = 16; o > 0; o >>= 1) npairs += __shfl_xor_sync(0xffffffffu, npairs, o);
     if ((threadIdx.x & 31) == 0 && npairs) atomicAdd(&ctl->force_pairs, (unsigned long long)npairs);
@@ -448,53 +574,35 @@ __global__ void __launch_bounds__(kTile) k_force_first(SweepArgs A) {
 // the fully-kicked (v,u) of its lower-index neighbours is strictly lower triangular, so
 // this fixed point exists, is unique, is reached after finitely many sweeps and IS the
 // result of the reference's sequential in-place sweep.
-// Updates are made in place (chaotic relaxation); a sweep that changes nothing proves
+// A sweep works through the work list its predecessor filled (tiles are appended once per
+// sweep, guarded by the atomicMax on their stamp); a sweep that appends nothing proves
 // that every particle was last computed from the final values.
 template <bool ADIA, bool UM>
 __global__ void __launch_bounds__(kTile) k_force_refine(SweepArgs A, int max_sweeps) {
+    __shared__ ForceSmem S;
     cg::grid_group grid = cg::this_grid();
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
-    const int ntiles = (A.na + kTile - 1) / kTile;
     const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
-    int epoch = A.epoch;          // stamp of the first sweep (k_force_first)
+    int epoch = A.epoch;          // stamp of the first sweep (k_force_first), which filled wl[(epoch + 1) & 1]
     int used = 1;
     while (true) {
-        const int prev_changed = *((volatile int *)&ctl->nchanged[epoch & 1]);
-        if (prev_changed == 0) break;
+        const int cur = (epoch + 1) & 1;
+        const int nwork = *((volatile int *)&ctl->nwork[cur]);
+        if (nwork == 0) break;
         if (used >= max_sweeps) {
             if (blockIdx.x == 0 && threadIdx.x == 0) raise(ctl, E_NOT_CONVERGED, -1);
             break;
         }
         epoch++;
         used++;
-        if (blockIdx.x == 0 && threadIdx.x == 0) ctl->nchanged[epoch & 1] = 0;
+        if (blockIdx.x == 0 && threadIdx.x == 0) ctl->nwork[(epoch + 1) & 1] = 0;   // the list this sweep fills
         grid.sync();
-        for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-            if (__ldcg(A.dirty + t) < epoch - 1) continue;
-            const int s = A.pad + t * kTile + threadIdx.x;
-            bool changed = false;
-            if (s < A.pad + A.na) {
-                double acc, dudt, Pi;
-                int jmin, jmax, npairs;
-                const double vi = A.vh[s], ui = A.uh[s];
-                force_eval<SEL_INDEX, ADIA, UM, true>(A.F, A.m0, s, lo, hi, Hb, A.F.x[s], A.F.idx[s], A.hO[s],
-                                                      A.rO[s], A.oO[s], vi, ui, A.Pstale[s], acc, dudt, Pi,
-                                                      jmin, jmax, npairs);
-                const double vf = __dadd_rn(vi, __dmul_rn(acc, A.half_dt));
-                const double uf = __dadd_rn(ui, __dmul_rn(dudt, A.half_dt));
-                const double vo = __ldcg(A.vn + s), uo = __ldcg(A.un + s);
-                changed = (__double_as_longlong(vf) != __double_as_longlong(vo)) ||
-                          (__double_as_longlong(uf) != __double_as_longlong(uo));
-                if (changed) {
-                    A.a[s] = acc;
-                    A.du[s] = dudt;
-                    __stcg(A.vn + s, vf);
-                    __stcg(A.un + s, uf);
-                    mark_dirty(A.dirty, A.pad, A.na, jmin, jmax, epoch);
-                }
-            }
-            if (__syncthreads_or(changed) && threadIdx.x == 0) atomicAdd(&ctl->nchanged[epoch & 1], 1);
+        for (int w = blockIdx.x; w < nwork; w += gridDim.x) {
+            const int tile = __ldcg(A.wl[cur] + w);
+            bool changed;
+            int npairs;
+            force_tile<SEL_INDEX, ADIA, UM, false>(A, S, tile, lo, hi, Hb, epoch, changed, npairs);
         }
         grid.sync();
     }
@@ -804,8 +912,8 @@ __global__ void k_begin(Ctl *ctl, int clear_cand) {
     ctl->hmax_bits = 0ull;
     ctl->unsorted = 0;
     if (clear_cand) ctl->ncand = 0;
-    ctl->nchanged[0] = 0;
-    ctl->nchanged[1] = 0;
+    ctl->nwork[0] = 0;
+    ctl->nwork[1] = 0;
     ctl->force_pairs = 0ull;
 }
 
