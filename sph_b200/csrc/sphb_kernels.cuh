@@ -71,18 +71,32 @@ __device__ __forceinline__ void raise(Ctl *ctl, int code, int particle) {
 // brings in are folded into the coefficients (exactly).
 __device__ __forceinline__ double clamp2(double t) { return t + fabs(t); }   // 2 * max(t, 0)
 
-// [-4 T1^3 + 20 T2^3 - 40 T3^3] for smoothing length h at distance r >= 0
+// [T1^3 - 5 T2^3 + 10 T3^3] = -(1/4) h^5 / sigma * w'(q)/h^2 for smoothing length h at distance r >= 0.
+// The FP64 pipe is what bounds the force pass, so the pieces are entered by branching on the SIGN
+// of t_k (an integer test of the high word, off the FP64 pipe) instead of clamping: a neighbour in
+// the outer shell costs 4 FP64 operations here, not 15.  Neighbouring lanes hold neighbouring
+// particles with nearly the same h and spacing, so the branches rarely diverge.
 __device__ __forceinline__ double dpoly(double r, double h) {
-    const double s1 = clamp2(fma(2.5, h, -r)), s2 = clamp2(fma(1.5, h, -r)), s3 = clamp2(fma(0.5, h, -r));
-    const double c1 = (s1 * s1) * s1, c2 = (s2 * s2) * s2, c3 = (s3 * s3) * s3;   // 8 T_k^3
-    return fma(-5.0, c3, fma(2.5, c2, -0.5 * c1));
+    const double t1 = fma(2.5, h, -r);
+    double p = 0.0;
+    if (__double2hiint(t1) >= 0) {
+        p = (t1 * t1) * t1;
+        const double t2 = fma(1.5, h, -r);
+        if (__double2hiint(t2) >= 0) {
+            p = fma(-5.0, (t2 * t2) * t2, p);
+            const double t3 = fma(0.5, h, -r);
+            if (__double2hiint(t3) >= 0) p = fma(10.0, (t3 * t3) * t3, p);
+        }
+    }
+    return p;
 }
+constexpr double kGradC = -4.0 * kSigma;   // w'(q)/h^2 = kGradC / h^5 * dpoly(r, h)
 
 // What the density pass leaves per particle for the force pass: everything a pair needs from
 // its neighbour without a division.
 struct __align__(32) Rec {
     double h;     // smoothing length
-    double c5;    // sigma / h^5
+    double c5;    // -4 sigma / h^5
     double rho;   // density
     double kap;   // 1 / (rho * omega):  P / (rho^2 omega) = (gamma - 1) u kap (adiabatic), kap (isothermal)
 };
@@ -100,54 +114,84 @@ constexpr int kFHalo = 32;    // force pass: neighbour state staged on each side
 // sx[-1] and sx[wn]; a scan that runs off the staged part goes on in global memory.  The scan
 // stops at the first particle outside the support: the array is x-sorted, so every farther
 // one is outside as well.
+// one neighbour at distance r (0 <= r < 2.5 h): adds its terms to sw, sg
+template <bool UM>
+__device__ __forceinline__ void density_term(double r, double a1, double a2, double a3, double mj, double &sw,
+                                             double &sg) {
+    const double t1 = a1 - r;
+    const double c1 = (t1 * t1) * t1;
+    const double r5 = 5.0 * r;
+    sw = fma(c1, t1, sw);
+    double g = c1 * (a1 - r5);
+    const double t2 = a2 - r;
+    if (__double2hiint(t2) >= 0) {                 // sign tests run off the FP64 pipe (see dpoly)
+        const double c2 = -5.0 * ((t2 * t2) * t2);
+        sw = fma(c2, t2, sw);
+        g = fma(c2, a2 - r5, g);
+        const double t3 = a3 - r;
+        if (__double2hiint(t3) >= 0) {
+            const double c3 = 10.0 * ((t3 * t3) * t3);
+            sw = fma(c3, t3, sw);
+            g = fma(c3, a3 - r5, g);
+        }
+    }
+    if (UM) sg += g; else sg = fma(mj, g, sg);
+}
+
+// one side (DIR = -1 left, +1 right) of the scan around sorted slot s
+template <bool UM, int DIR>
+__device__ __forceinline__ void density_side(const double *sx, int wbase, int wn, const double *__restrict__ gx,
+                                             const double *__restrict__ m, int s, int lo, int hi, double xi,
+                                             double h, double a1, double a2, double a3, double r_in, double &sw,
+                                             double &sg, int &c) {
+    int k = s - wbase + DIR;
+    double r;
+#pragma unroll 1
+    while (true) {                                  // staged part; the +-INF sentinels end it
+        r = DIR > 0 ? (sx[k] - xi) : (xi - sx[k]);
+        if (!(r < r_in)) break;
+        c++;
+        density_term<UM>(r, a1, a2, a3, UM ? 0.0 : __ldg(m + wbase + k), sw, sg);
+        k += DIR;
+    }
+    // From here on r >= r_in (x is sorted): only particles within rounding of the support edge can
+    // still count (kernel.cpp:31 decides with an IEEE division); they contribute < 1e-57 h^4.
+#pragma unroll 1
+    while (k >= 0 && k < wn) {
+        if (!(r / h < kRadius)) return;
+        c++;
+        k += DIR;
+        r = DIR > 0 ? (sx[k] - xi) : (xi - sx[k]);
+    }
+    // rare: the scan ran off the staged part (more than kDHalo neighbours on this side)
+#pragma unroll 1
+    for (int j = wbase + k; j >= lo && j < hi; j += DIR) {
+        r = DIR > 0 ? (__ldg(gx + j) - xi) : (xi - __ldg(gx + j));
+        if (r < r_in) {
+            c++;
+            density_term<UM>(r, a1, a2, a3, UM ? 0.0 : __ldg(m + j), sw, sg);
+        } else if (r / h < kRadius) {
+            c++;
+        } else {
+            return;
+        }
+    }
+}
+
 template <bool UM>
 __device__ __forceinline__ void density_sums(const double *sx, int wbase, int wn, const double *__restrict__ gx,
                                              const double *__restrict__ m, int s, int lo, int hi, double xi,
                                              double h, double &Sw, double &Sg, int &cnt) {
     const double a1 = 2.5 * h, a2 = 1.5 * h, a3 = 0.5 * h;
-    const double r_in = a1 * (1.0 - 0x1p-48);     // below: certainly inside; from here on decide exactly
-    double sw16 = 0.0, sg8 = 0.0;                 // sums over j != i in units of s_k = 2 T_k
-    int c = 1;
-#pragma unroll 1
-    for (int side = 0; side < 2; side++) {
-        const int step = side ? 1 : -1;
-        int k = s - wbase + step;
-        bool staged = true;
-#pragma unroll 1
-        while (true) {
-            double xj;
-            if (staged) {
-                xj = sx[k];
-            } else {
-                const int j = wbase + k;
-                if (j < lo || j >= hi) break;
-                xj = __ldg(gx + j);
-            }
-            const double r = side ? (xj - xi) : (xi - xj);
-            if (!(r < r_in)) {
-                if (staged && (k < 0 || k >= wn)) {       // sentinel: end of the staged part ...
-                    const int j = wbase + k;
-                    if (j < lo || j >= hi) break;         // ... which is also the end of the array
-                    staged = false;                       // rare: more than kDHalo neighbours on one side
-                    continue;
-                }
-                if (r / h < kRadius) { c++; k += step; continue; }   // on the edge: counts, contributes < 1e-57 h^4
-                break;
-            }
-            c++;
-            const double s1 = clamp2(a1 - r), s2 = clamp2(a2 - r), s3 = clamp2(a3 - r);
-            const double c1 = (s1 * s1) * s1, c2 = -5.0 * ((s2 * s2) * s2), c3 = 10.0 * ((s3 * s3) * s3);
-            const double r5 = 5.0 * r;
-            sw16 = fma(c3, s3, fma(c2, s2, fma(c1, s1, sw16)));
-            const double g = fma(c3, a3 - r5, fma(c2, a2 - r5, c1 * (a1 - r5)));
-            if (UM) sg8 += g; else sg8 = fma(__ldg(m + wbase + k), g, sg8);
-            k += step;
-        }
-    }
+    const double r_in = a1 * (1.0 - 0x1p-48);     // below: certainly inside; from there on decide exactly
     const double h2 = h * h;
     const double self = 14.375 * (h2 * h2);       // r = 0: (5/2)^4 - 5 (3/2)^4 + 10 (1/2)^4, times h^4
-    Sw = fma(0.0625, sw16, self);
-    Sg = UM ? fma(0.125, sg8, self) : fma(0.125, sg8, self * __ldg(m + s));
+    double sw = self, sg = UM ? self : self * __ldg(m + s);
+    int c = 1;
+    density_side<UM, -1>(sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, c);
+    density_side<UM, +1>(sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, c);
+    Sw = sw;
+    Sg = sg;
     cnt = c;
 }
 
@@ -287,15 +331,15 @@ __global__ void __launch_bounds__(kTile) k_density(DensityArgs A) {
         A.rhon[s] = rhonew;
         if (A.omn) { A.omn[s] = om_new; A.oms[s] = om_stale; }
         if (A.recA) {
-            // c5 = sigma / h^5 and kap = 1 / (rho omega): the only divisions the force pass would need
+            // c5 = -4 sigma / h^5 and kap = 1 / (rho omega): the only divisions the force pass would need
             const double ihn = 1.0 / hnew, ihn2 = ihn * ihn;
             Rec ra;
-            ra.h = hnew; ra.c5 = kSigma * ((ihn2 * ihn2) * ihn); ra.rho = rhonew; ra.kap = 1.0 / (rhonew * om_new);
+            ra.h = hnew; ra.c5 = kGradC * ((ihn2 * ihn2) * ihn); ra.rho = rhonew; ra.kap = 1.0 / (rhonew * om_new);
             A.recA[s] = ra;
             Rec rb = ra;
             if (VARH && A.check_old) {
                 const double iho = 1.0 / hold, iho2 = iho * iho;
-                rb.h = hold; rb.c5 = kSigma * ((iho2 * iho2) * iho); rb.rho = rhoold; rb.kap = 1.0 / (rhoold * om_stale);
+                rb.h = hold; rb.c5 = kGradC * ((iho2 * iho2) * iho); rb.rho = rhoold; rb.kap = 1.0 / (rhoold * om_stale);
             } else if (A.check_old) {
                 rb.rho = rhoold; rb.kap = 1.0 / rhoold;      // fixed h: omega = 1, h unchanged
             }
@@ -388,7 +432,7 @@ __device__ __forceinline__ bool pair_terms(const Own<ADIA> &o, double ar, double
     const double iD = t * rs;
     const double irs = t * D;
     const double ihb2 = ihb * ihb;
-    const double gb = dpoly(ar, hb) * (kSigma * ((ihb2 * ihb2) * ihb));     // |gradW(hbar)| with its own sign of w'
+    const double gb = dpoly(ar, hb) * (kGradC * ((ihb2 * ihb2) * ihb));     // |gradW(hbar)| with its own sign of w'
     const double PrRho_j = ADIA ? ((kGamma - 1) * uj) * rj.kap : rj.kap;
     const double gi = dpoly(ar, o.h) * o.Ci;
     const double gj = dpoly(ar, hj) * (rj.c5 * PrRho_j);
@@ -423,12 +467,65 @@ struct ForceSmem {
 template <bool VOL>
 __device__ __forceinline__ double ldv(const double *p) { return VOL ? __ldcg(p) : __ldg(p); }
 
+template <int SEL>
+__device__ __forceinline__ bool sees_new_state(unsigned idxj, unsigned idxi) {
+    if (SEL == SEL_INDEX) return idxj < idxi;            // the reference's sweep has already updated j
+    if (SEL == SEL_ALIVE) return !(idxj & kGhostBit);
+    return true;
+}
+
+// All neighbours on one side (DIR = -1: left, x_j <= x_i; +1: right) of particle `o`, staged part
+// first, then (rarely) global memory.  gradW carries sign(x_i - x_j) (calculators.cpp:17-27): the
+// unsigned sums of this side enter a with -DIR... i.e. a -= accA on the left, a += accA on the right,
+// and du/dt with the opposite signs.  `jend` receives the farthest slot within reach.
+template <int SEL, bool ADIA, bool UM, bool FIRST, int DIR>
+__device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &S, const Own<ADIA> &o, int ks,
+                                           int wbase, int wn, int lo, int hi, double reach, double &a_sum,
+                                           double &e_sum, int &npairs, int &jend) {
+    const double *sx = S.x + 1;
+    const double dir = DIR > 0 ? -1.0 : 1.0;      // sign of x_i - x_j
+    double accA = 0.0, accE = 0.0;
+    int k = ks + DIR;
+#pragma unroll 1
+    while (true) {
+        const double ar = DIR > 0 ? (sx[k] - o.x) : (o.x - sx[k]);
+        if (!(ar < reach)) break;                 // also the +-INF sentinels
+        const bool useA = sees_new_state<SEL>(S.idx[k], o.idx);
+        const Rec rj = useA ? S.rA[k] : S.rB[k];
+        const double vj = (useA && !FIRST) ? S.vA[k] : S.vB[k];
+        const double uj = (useA && !FIRST) ? S.uA[k] : S.uB[k];
+        const double mj = UM ? 0.0 : __ldg(A.F.m + wbase + k);
+        if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
+        k += DIR;
+    }
+    int j = wbase + k;                            // first particle not handled above
+    if ((k < 0 || k >= wn) && j >= lo && j < hi) {
+        // rare: the reach extends beyond the staged halo — continue in global memory
+#pragma unroll 1
+        for (; j >= lo && j < hi; j += DIR) {
+            const double xj = __ldg(A.F.x + j);
+            const double ar = DIR > 0 ? (xj - o.x) : (o.x - xj);
+            if (!(ar < reach)) break;
+            const bool useA = sees_new_state<SEL>(__ldg(A.F.idx + j), o.idx);
+            const Rec rj = useA ? A.F.recA[j] : A.F.recB[j];
+            const double vj = (useA && !FIRST) ? ldv<true>(A.F.vA + j) : __ldg(A.F.vB + j);
+            const double uj = (useA && !FIRST) ? ldv<true>(A.F.uA + j) : __ldg(A.F.uB + j);
+            const double mj = UM ? 0.0 : __ldg(A.F.m + j);
+            if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
+        }
+    }
+    jend = j - DIR;
+    a_sum = DIR > 0 ? (a_sum + accA) : (a_sum - accA);
+    e_sum = DIR > 0 ? (e_sum - accE) : (e_sum + accE);
+}
+
 // Evaluate one tile: stage, compute a, du/dt (and the kick), store.  Returns through
 // `changed_any` whether any particle's kicked (v, u) differs from what was stored before.
 // FIRST: sweep 1 of a step (vA == vB: everybody is seen half-kicked, outputs always stored).
 template <int SEL, bool ADIA, bool UM, bool FIRST>
-__device__ __forceinline__ void force_tile(const SweepArgs &A, ForceSmem &S, int tile, int lo, int hi, double Hb,
+__device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo, int hi, double Hb,
                                            int epoch, bool &changed_any, int &npairs_out) {
+    __shared__ ForceSmem S;
     const int t0 = A.pad + tile * kTile;
     const int tend = min(t0 + kTile, A.pad + A.na);
     const int wbase = max(t0 - kFHalo, lo);
@@ -460,56 +557,8 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, ForceSmem &S, int
         double a_sum = 0.0, e_sum = 0.0;
         int jmin = s, jmax = s;
         npairs = 1;   // self: its energy term is evaluated by the reference too (and is exactly 0)
-#pragma unroll 1
-        for (int side = 0; side < 2; side++) {
-            const int step = side ? 1 : -1;
-            const double dir = side ? -1.0 : 1.0;
-            double accA = 0.0, accE = 0.0;
-            int k = ks + step;
-#pragma unroll 1
-            while (true) {                              // staged part
-                const double ar = side ? (sx[k] - o.x) : (o.x - sx[k]);
-                if (!(ar < reach)) break;               // also the +-INF sentinels
-                const unsigned idxj = S.idx[k];
-                bool useA;
-                if (SEL == SEL_INDEX) useA = idxj < o.idx;
-                else if (SEL == SEL_ALIVE) useA = !(idxj & kGhostBit);
-                else useA = true;
-                const Rec rj = useA ? S.rA[k] : S.rB[k];
-                const double vj = (useA && !FIRST) ? S.vA[k] : S.vB[k];
-                const double uj = (useA && !FIRST) ? S.uA[k] : S.uB[k];
-                const double mj = UM ? 0.0 : __ldg(A.F.m + wbase + k);
-                if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
-                k += step;
-            }
-            int j = wbase + k;                          // first particle not handled above
-            if ((k < 0 || k >= wn) && j >= lo && j < hi) {
-                // rare: the support reaches beyond the staged halo — continue in global memory
-#pragma unroll 1
-                for (; j >= lo && j < hi; j += step) {
-                    const double xj = __ldg(A.F.x + j);
-                    const double ar = side ? (xj - o.x) : (o.x - xj);
-                    if (!(ar < reach)) break;
-                    const unsigned idxj = __ldg(A.F.idx + j);
-                    bool useA;
-                    if (SEL == SEL_INDEX) useA = idxj < o.idx;
-                    else if (SEL == SEL_ALIVE) useA = !(idxj & kGhostBit);
-                    else useA = true;
-                    const Rec rj = useA ? A.F.recA[j] : A.F.recB[j];
-                    const double vj = (useA && !FIRST) ? ldv<true>(A.F.vA + j) : __ldg(A.F.vB + j);
-                    const double uj = (useA && !FIRST) ? ldv<true>(A.F.uA + j) : __ldg(A.F.uB + j);
-                    const double mj = UM ? 0.0 : __ldg(A.F.m + j);
-                    if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
-                }
-                j -= step;
-            } else {
-                j -= step;
-            }
-            if (side) jmax = max(j, s); else jmin = min(j, s);
-            // gradW carries sign(x_i - x_j) (calculators.cpp:17-27): + for left neighbours, - for right
-            a_sum = side ? (a_sum + accA) : (a_sum - accA);
-            e_sum = side ? (e_sum - accE) : (e_sum + accE);
-        }
+        force_side<SEL, ADIA, UM, FIRST, -1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmin);
+        force_side<SEL, ADIA, UM, FIRST, +1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmax);
         if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
         if (!A.kick) {
             A.a[s] = a_sum;
@@ -556,13 +605,12 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, ForceSmem &S, int
 // jacobi order and for the kick-less t = 0 pass).
 template <int SEL, bool ADIA, bool UM>
 __global__ void __launch_bounds__(kTile) k_force_first(SweepArgs A) {
-    __shared__ ForceSmem S;
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
     const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
     bool changed;
     int npairs;
-    force_tile<SEL, ADIA, UM, true>(A, S, blockIdx.x, lo, hi, Hb, A.epoch, changed, npairs);
+    force_tile<SEL, ADIA, UM, true>(A, blockIdx.x, lo, hi, Hb, A.epoch, changed, npairs);
     // pair statistics for the roofline accounting (one atomic per warp)
     for (int o = 16; o > 0; o >>= 1) npairs += __shfl_xor_sync(0xffffffffu, npairs, o);
     if ((threadIdx.x & 31) == 0 && npairs) atomicAdd(&ctl->force_pairs, (unsigned long long)npairs);
@@ -579,7 +627,6 @@ __global__ void __launch_bounds__(kTile) k_force_first(SweepArgs A) {
 // that every particle was last computed from the final values.
 template <bool ADIA, bool UM>
 __global__ void __launch_bounds__(kTile) k_force_refine(SweepArgs A, int max_sweeps) {
-    __shared__ ForceSmem S;
     cg::grid_group grid = cg::this_grid();
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
@@ -602,7 +649,7 @@ __global__ void __launch_bounds__(kTile) k_force_refine(SweepArgs A, int max_swe
             const int tile = __ldcg(A.wl[cur] + w);
             bool changed;
             int npairs;
-            force_tile<SEL_INDEX, ADIA, UM, false>(A, S, tile, lo, hi, Hb, epoch, changed, npairs);
+            force_tile<SEL_INDEX, ADIA, UM, false>(A, tile, lo, hi, Hb, epoch, changed, npairs);
         }
         grid.sync();
     }
