@@ -36,7 +36,8 @@ struct sphb_handle {
     unsigned *idx = nullptr, *idx_alt = nullptr;
     int *slot_id = nullptr, *cnt = nullptr, *dirty = nullptr, *cand = nullptr, *gorder = nullptr,
         *perm = nullptr, *iota = nullptr, *wl0 = nullptr, *wl1 = nullptr;
-    Rec *recA = nullptr, *recB = nullptr;   // force-pass records written by the density pass
+    Rec2 *rec = nullptr;      // force-pass records written by the density pass
+    double *gsum = nullptr;   // own-h gradient sums written by the density pass
     // ghost staging (2*pad each)
     double *gx = nullptr, *gv = nullptr, *gu = nullptr, *ga = nullptr, *gdu = nullptr, *gh = nullptr,
            *grho = nullptr, *gP = nullptr, *gm = nullptr;
@@ -234,7 +235,7 @@ int launch_density(sphb_handle *H, int root_alive, int root_ghosts, int check_ol
     A.x = H->x; A.m = H->m; A.h = H->h; A.rho = H->rho; A.P = H->P;
     A.hn = H->hn; A.rhon = H->rhon; A.Pn = Pn;
     A.omn = want_omega ? H->omn : nullptr; A.oms = want_omega ? H->oms : nullptr;
-    A.recA = H->recA; A.recB = H->recB;
+    A.rec = H->rec; A.gsum = H->gsum;
     A.cnt = H->cnt; A.ctl = H->d_ctl; A.pad = H->pad; A.na = H->na;
     A.limit = H->cfg.limit; A.hfac = H->cfg.h_factor; A.m0 = H->m0;
     A.root_ghosts = root_ghosts; A.root_alive = root_alive; A.check_old = check_old;
@@ -287,7 +288,7 @@ int launch_refine(sphb_handle *H, SweepArgs A) {
 SweepArgs sweep_args(sphb_handle *H) {
     SweepArgs A;
     A.F.x = H->x; A.F.idx = H->idx; A.F.m = H->m;
-    A.F.recA = H->recA; A.F.recB = H->recB;
+    A.F.rec = H->rec; A.F.gsum = H->gsum;
     A.a = H->a; A.du = H->du; A.dirty = H->dirty; A.wl[0] = H->wl0; A.wl[1] = H->wl1; A.ctl = H->d_ctl;
     A.pad = H->pad; A.na = H->na; A.m0 = H->m0; A.half_dt = H->cfg.t_i / 2;
     A.epoch = H->epoch; A.kick = 1;
@@ -484,7 +485,7 @@ int sphb_create(const sphb_config *cfg, const sphb_options *opt_in, sphb_handle 
     rc |= dalloc(H, &H->perm, (size_t)H->cap_alive); rc |= dalloc(H, &H->iota, (size_t)H->cap_alive);
     rc |= dalloc(H, &H->gkey, (size_t)H->cand_cap); rc |= dalloc(H, &H->d_ctl, 1);
     rc |= dalloc(H, &H->wl0, (size_t)nblk(H->cap_alive, kTile) + 1); rc |= dalloc(H, &H->wl1, (size_t)nblk(H->cap_alive, kTile) + 1);
-    rc |= dalloc(H, &H->recA, T); rc |= dalloc(H, &H->recB, T);
+    rc |= dalloc(H, &H->rec, T); rc |= dalloc(H, &H->gsum, T);
     if (rc) return fail(SPHB_ERR_CUDA);
     CKC(cudaMallocHost((void **)&H->h_ctl, sizeof(Ctl)));
     memset(H->h_ctl, 0, sizeof(Ctl));
@@ -508,7 +509,7 @@ void sphb_destroy(sphb_handle *H) {
                     H->hn, H->rhon, H->omn, H->oms, H->Pn, H->tmp, H->gx, H->gv, H->gu, H->ga, H->gdu, H->gh,
                     H->grho, H->gP, H->gm, H->idx, H->idx_alt, H->slot_id, H->cnt, H->dirty, H->cand, H->gorder,
                     H->perm, H->iota, H->gkey, H->d_ctl, H->cub_tmp, H->d_aos, H->d_newton, H->d_nbr,
-                    H->wl0, H->wl1, H->recA, H->recB};
+                    H->wl0, H->wl1, H->rec, H->gsum};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (H->h_ctl) cudaFreeHost(H->h_ctl);
     for (int i = 0; i <= SPHB_PHASES; i++) if (H->ev[i]) cudaEventDestroy(H->ev[i]);
@@ -870,7 +871,7 @@ int sphb_density_static(const double *d_x, const double *d_h, const double *d_rh
     DensityArgs A;
     A.x = d_x; A.m = nullptr; A.h = d_h; A.rho = d_rho; A.P = nullptr;
     A.hn = d_h_out; A.rhon = d_rho_out; A.omn = om_new; A.oms = om_stale; A.Pn = nullptr;
-    A.recA = nullptr; A.recB = nullptr;
+    A.rec = nullptr; A.gsum = nullptr;
     A.cnt = cnt; A.ctl = ctl; A.pad = 0; A.na = n;
     A.limit = limit; A.hfac = h_factor; A.m0 = mass;
     A.root_ghosts = 0; A.root_alive = 1; A.check_old = 0;

@@ -76,15 +76,14 @@ __device__ __forceinline__ double clamp2(double t) { return t + fabs(t); }   // 
 // of t_k (an integer test of the high word, off the FP64 pipe) instead of clamping: a neighbour in
 // the outer shell costs 4 FP64 operations here, not 15.  Neighbouring lanes hold neighbouring
 // particles with nearly the same h and spacing, so the branches rarely diverge.
-__device__ __forceinline__ double dpoly(double r, double h) {
-    const double t1 = fma(2.5, h, -r);
+__device__ __forceinline__ double dpoly_from(double t1, double r, double h, double k2, double k3) {
     double p = 0.0;
     if (__double2hiint(t1) >= 0) {
         p = (t1 * t1) * t1;
-        const double t2 = fma(1.5, h, -r);
+        const double t2 = fma(k2, h, -r);
         if (__double2hiint(t2) >= 0) {
             p = fma(-5.0, (t2 * t2) * t2, p);
-            const double t3 = fma(0.5, h, -r);
+            const double t3 = fma(k3, h, -r);
             if (__double2hiint(t3) >= 0) p = fma(10.0, (t3 * t3) * t3, p);
         }
     }
@@ -101,6 +100,8 @@ struct __align__(32) Rec {
     double kap;   // 1 / (rho * omega):  P / (rho^2 omega) = (gamma - 1) u kap (adiabatic), kap (isothermal)
 };
 
+struct __align__(64) Rec2 { Rec A, B; };   // new state (as seen once the sweep has passed) / old state
+
 constexpr int kDHalo = 64;    // density pass: x staged on each side of a tile
 constexpr int kFHalo = 32;    // force pass: neighbour state staged on each side of a tile
 
@@ -109,6 +110,7 @@ constexpr int kFHalo = 32;    // force pass: neighbour state staged on each side
 // window, self included:
 //   Sw = sum_j [T1^4 - 5 T2^4 + 10 T3^4]           so that  sum_j w(q_j)              = sigma/h^4 Sw
 //   Sg = sum_j m_j [T1^3 (a1 h - 5 r) - ...]        so that  sum_j m_j (w + q w')(q_j) = sigma/h^4 Sg
+//   Sgr = sum_j m_j sign(x_i - x_j) [T1^3 - 5 T2^3 + 10 T3^3]   so that  sum_j m_j gradW_ij(h) = -4 sigma/h^5 Sgr
 //   cnt = #{ j : |x_i - x_j| / h < 2.5 }            with the reference's IEEE division (kernel.cpp:31)
 // sx is the staged window, sx[k] = x[wbase + k] for 0 <= k < wn, with +-INF sentinels at
 // sx[-1] and sx[wn]; a scan that runs off the staged part goes on in global memory.  The scan
@@ -117,25 +119,28 @@ constexpr int kFHalo = 32;    // force pass: neighbour state staged on each side
 // one neighbour at distance r (0 <= r < 2.5 h): adds its terms to sw, sg
 template <bool UM>
 __device__ __forceinline__ void density_term(double r, double a1, double a2, double a3, double mj, double &sw,
-                                             double &sg) {
+                                             double &sg, double &sgr) {
     const double t1 = a1 - r;
     const double c1 = (t1 * t1) * t1;
     const double r5 = 5.0 * r;
     sw = fma(c1, t1, sw);
     double g = c1 * (a1 - r5);
+    double d = c1;                                 // T1^3 - 5 T2^3 + 10 T3^3: the gradient's polynomial
     const double t2 = a2 - r;
-    if (__double2hiint(t2) >= 0) {                 // sign tests run off the FP64 pipe (see dpoly)
+    if (__double2hiint(t2) >= 0) {                 // sign tests run off the FP64 pipe (see dpoly_from)
         const double c2 = -5.0 * ((t2 * t2) * t2);
         sw = fma(c2, t2, sw);
         g = fma(c2, a2 - r5, g);
+        d += c2;
         const double t3 = a3 - r;
         if (__double2hiint(t3) >= 0) {
             const double c3 = 10.0 * ((t3 * t3) * t3);
             sw = fma(c3, t3, sw);
             g = fma(c3, a3 - r5, g);
+            d += c3;
         }
     }
-    if (UM) sg += g; else sg = fma(mj, g, sg);
+    if (UM) { sg += g; sgr += d; } else { sg = fma(mj, g, sg); sgr = fma(mj, d, sgr); }
 }
 
 // one side (DIR = -1 left, +1 right) of the scan around sorted slot s
@@ -143,7 +148,7 @@ template <bool UM, int DIR>
 __device__ __forceinline__ void density_side(const double *sx, int wbase, int wn, const double *__restrict__ gx,
                                              const double *__restrict__ m, int s, int lo, int hi, double xi,
                                              double h, double a1, double a2, double a3, double r_in, double &sw,
-                                             double &sg, int &c) {
+                                             double &sg, double &sgr, int &c) {
     int k = s - wbase + DIR;
     double r;
 #pragma unroll 1
@@ -151,7 +156,7 @@ __device__ __forceinline__ void density_side(const double *sx, int wbase, int wn
         r = DIR > 0 ? (sx[k] - xi) : (xi - sx[k]);
         if (!(r < r_in)) break;
         c++;
-        density_term<UM>(r, a1, a2, a3, UM ? 0.0 : __ldg(m + wbase + k), sw, sg);
+        density_term<UM>(r, a1, a2, a3, UM ? 0.0 : __ldg(m + wbase + k), sw, sg, sgr);
         k += DIR;
     }
     // From here on r >= r_in (x is sorted): only particles within rounding of the support edge can
@@ -169,7 +174,7 @@ __device__ __forceinline__ void density_side(const double *sx, int wbase, int wn
         r = DIR > 0 ? (__ldg(gx + j) - xi) : (xi - __ldg(gx + j));
         if (r < r_in) {
             c++;
-            density_term<UM>(r, a1, a2, a3, UM ? 0.0 : __ldg(m + j), sw, sg);
+            density_term<UM>(r, a1, a2, a3, UM ? 0.0 : __ldg(m + j), sw, sg, sgr);
         } else if (r / h < kRadius) {
             c++;
         } else {
@@ -181,17 +186,19 @@ __device__ __forceinline__ void density_side(const double *sx, int wbase, int wn
 template <bool UM>
 __device__ __forceinline__ void density_sums(const double *sx, int wbase, int wn, const double *__restrict__ gx,
                                              const double *__restrict__ m, int s, int lo, int hi, double xi,
-                                             double h, double &Sw, double &Sg, int &cnt) {
+                                             double h, double &Sw, double &Sg, double &Sgr, int &cnt) {
     const double a1 = 2.5 * h, a2 = 1.5 * h, a3 = 0.5 * h;
     const double r_in = a1 * (1.0 - 0x1p-48);     // below: certainly inside; from there on decide exactly
     const double h2 = h * h;
     const double self = 14.375 * (h2 * h2);       // r = 0: (5/2)^4 - 5 (3/2)^4 + 10 (1/2)^4, times h^4
     double sw = self, sg = UM ? self : self * __ldg(m + s);
     int c = 1;
-    density_side<UM, -1>(sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, c);
-    density_side<UM, +1>(sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, c);
+    double grl = 0.0, grr = 0.0;
+    density_side<UM, -1>(sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, grl, c);
+    density_side<UM, +1>(sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, grr, c);
     Sw = sw;
     Sg = sg;
+    Sgr = grl - grr;                              // gradW carries sign(x_i - x_j): + for left neighbours
     cnt = c;
 }
 
@@ -199,7 +206,8 @@ struct DensityArgs {
     const double *x, *m, *h, *rho, *P;
     double *hn, *rhon, *Pn;
     double *omn, *oms;   // omega for the new / the old (h, rho) at the new positions; may be null
-    Rec *recA, *recB;    // force-pass records of the new / the old state; may be null
+    Rec2 *rec;           // force-pass records of the new and the old state; may be null
+    double *gsum;        // sum_j m_j gradW_ij(h_i^new): the acceleration's own-h term; null iff rec is null
     int *cnt;            // (newton_iters << 24) | neighbour count
     Ctl *ctl;
     int pad, na;
@@ -218,7 +226,7 @@ struct DensityArgs {
 // derivative sum gives omega_stale = calc_omega(old h, old rho) at the new positions.
 // With f(h) = m_i sigma Sw / h^5 - m_i hf / h and f'(h) = -sigma Sg / h^6 + m_i hf / h^2.
 template <bool VARH, bool UM>
-__global__ void __launch_bounds__(kTile) k_density(DensityArgs A) {
+__global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
     __shared__ double sxs[kTile + 2 * kDHalo + 2];
     double *sx = sxs + 1;
     Ctl *ctl = A.ctl;
@@ -243,10 +251,10 @@ __global__ void __launch_bounds__(kTile) k_density(DensityArgs A) {
         const int npart = A.na + ctl->GL + ctl->GR;
         double hnew = hold, rhonew = rhoold, om_new = 1.0, om_stale = 1.0;
         int iters = 0, cnt = 0;
-        double Sw, Sg;
+        double Sw, Sg, Sgr = 0.0;
 #define SPHB_EVAL(H_, F_, DF_, DSUM_)                                                           \
     {                                                                                           \
-        density_sums<UM>(sx, wbase, wn, A.x, A.m, s, lo, hi, xi, (H_), Sw, Sg, cnt);            \
+        density_sums<UM>(sx, wbase, wn, A.x, A.m, s, lo, hi, xi, (H_), Sw, Sg, Sgr, cnt);       \
         const double ih_ = 1.0 / (H_), ih2_ = ih_ * ih_, ih4_ = ih2_ * ih2_;                    \
         const double rho_ = mi * (kSigma * (Sw * (ih4_ * ih_)));                                \
         F_ = rho_ - mi * A.hfac * ih_;                                                          \
@@ -330,20 +338,21 @@ __global__ void __launch_bounds__(kTile) k_density(DensityArgs A) {
         A.hn[s] = hnew;
         A.rhon[s] = rhonew;
         if (A.omn) { A.omn[s] = om_new; A.oms[s] = om_stale; }
-        if (A.recA) {
+        if (A.rec) {
             // c5 = -4 sigma / h^5 and kap = 1 / (rho omega): the only divisions the force pass would need
             const double ihn = 1.0 / hnew, ihn2 = ihn * ihn;
-            Rec ra;
-            ra.h = hnew; ra.c5 = kGradC * ((ihn2 * ihn2) * ihn); ra.rho = rhonew; ra.kap = 1.0 / (rhonew * om_new);
-            A.recA[s] = ra;
-            Rec rb = ra;
+            Rec2 r2;
+            r2.A.h = hnew; r2.A.c5 = kGradC * ((ihn2 * ihn2) * ihn); r2.A.rho = rhonew; r2.A.kap = 1.0 / (rhonew * om_new);
+            r2.B = r2.A;
             if (VARH && A.check_old) {
                 const double iho = 1.0 / hold, iho2 = iho * iho;
-                rb.h = hold; rb.c5 = kGradC * ((iho2 * iho2) * iho); rb.rho = rhoold; rb.kap = 1.0 / (rhoold * om_stale);
+                r2.B.h = hold; r2.B.c5 = kGradC * ((iho2 * iho2) * iho); r2.B.rho = rhoold; r2.B.kap = 1.0 / (rhoold * om_stale);
             } else if (A.check_old) {
-                rb.rho = rhoold; rb.kap = 1.0 / rhoold;      // fixed h: omega = 1, h unchanged
+                r2.B.rho = rhoold; r2.B.kap = 1.0 / rhoold;      // fixed h: omega = 1, h unchanged
             }
-            A.recB[s] = rb;
+            A.rec[s] = r2;
+            // Sgr belongs to the LAST evaluation, which was at hnew (or at the stored h when nothing was root-found)
+            A.gsum[s] = (UM ? mi : 1.0) * (r2.A.c5 * Sgr);
         }
         if (A.root_alive || A.root_ghosts) A.cnt[s] = (iters << 24) | (cnt & 0xffffff);
         if (is_pad && A.Pn != A.P) A.Pn[s] = A.P[s];
@@ -374,7 +383,8 @@ struct ForceArrays {
     const double *x;
     const unsigned *idx;
     const double *m;
-    const Rec *recA, *recB;
+    const Rec2 *rec;
+    const double *gsum;        // sum_j m_j gradW_ij(h_i) from the density pass
     const double *vA, *uA;     // current iterate of the fully kicked v, u (read with .cg: other CTAs update it)
     const double *vB, *uB;     // half-kicked base state
 };
@@ -400,7 +410,7 @@ struct SweepArgs {
 // per-thread invariants of one force evaluation
 template <bool ADIA>
 struct Own {
-    double x, h, rho, v, PrRho, Ci, c_ac, c_ec, P;
+    double x, h, rho, v, PrRho, c_ac, c_ec, P;
     unsigned idx;
     __device__ __forceinline__ void set(double xi, unsigned idxi, const Rec &r, double vi, double ui, double Pstale) {
         x = xi; idx = idxi; h = r.h; rho = r.rho; v = vi;
@@ -408,46 +418,47 @@ struct Own {
         c_ac = ADIA ? sqrt(kGamma * Pstale / r.rho) : 1.0;              // stale stored pressure
         c_ec = ADIA ? sqrt(kGamma * P / r.rho) : 1.0;                   // fresh pressure
         PrRho = ADIA ? ((kGamma - 1) * ui) * r.kap : r.kap;             // P_i / (rho_i^2 omega_i)
-        Ci = PrRho * r.c5;
     }
 };
 
-// One (i, j) pair; ar = |x_i - x_j| >= 0 and the sign of the gradient is applied by the
-// caller per side.  accA gathers m_j [gradW(h_i) P_i/(rho_i^2 om_i) + gradW(h_j) P_j/(rho_j^2 om_j)
+// One (i, j) pair; ar = |x_i - x_j| >= 0 and the sign of the gradient is applied by the caller per
+// side.  The acceleration's first term, gradW(h_i) P_i/(rho_i^2 om_i), does not depend on j's state:
+// its sum over j comes from the density pass (gsum).  accA gathers m_j [gradW(h_j) P_j/(rho_j^2 om_j)
 // + gradW(hbar) Pi_ij(c_ac)], accE gathers m_j v_ij gradW(hbar) [P_i/(rho_i^2 om_i) + Pi_ij(c_ec)/2],
 // both without the sign.  dir = +1 for a left neighbour (x_i - x_j = +ar), -1 for a right one.
+// Everything is written with hs = h_i + h_j = 2 hbar.
 template <bool ADIA, bool UM>
 __device__ __forceinline__ bool pair_terms(const Own<ADIA> &o, double ar, double dir, const Rec &rj, double vj,
                                            double uj, double mj, double &accA, double &accE) {
-    const double hj = rj.h;
-    if (ar >= kRadius * fmax(o.h, hj)) return false;     // all three gradients vanish
-    const double hb = 0.5 * (o.h + hj);
+    const double hs = o.h + rj.h;
+    const double t1j = fma(2.5, rj.h, -ar), t1b = fma(1.25, hs, -ar);
+    if ((__double2hiint(t1j) & __double2hiint(t1b)) < 0) return false;   // beyond 2.5 h_j and 2.5 hbar
     const double rs = o.rho + rj.rho;
-    const double D = fma(ar, ar, 0.01 * (hb * hb));
+    const double D = fma(ar, ar, 0.0025 * (hs * hs));        // r^2 + 0.01 hbar^2
     // one reciprocal serves 1/hbar, 1/D and 1/(rho_i + rho_j)
     const double DP = D * rs;
-    const double R = 1.0 / (hb * DP);
-    const double ihb = R * DP;
-    const double t = R * hb;              // 1 / (D rs)
+    const double R = 1.0 / (hs * DP);
+    const double ihs = R * DP;
+    const double t = R * hs;              // 1 / (D rs)
     const double iD = t * rs;
     const double irs = t * D;
-    const double ihb2 = ihb * ihb;
-    const double gb = dpoly(ar, hb) * (kGradC * ((ihb2 * ihb2) * ihb));     // |gradW(hbar)| with its own sign of w'
+    const double ihs2 = ihs * ihs;
+    // gradW(hbar) without its sign: -4 sigma / hbar^5 * poly = -128 sigma / hs^5 * poly
+    const double gb = dpoly_from(t1b, ar, hs, 0.75, 0.25) * ((32.0 * kGradC) * ((ihs2 * ihs2) * ihs));
     const double PrRho_j = ADIA ? ((kGamma - 1) * uj) * rj.kap : rj.kap;
-    const double gi = dpoly(ar, o.h) * o.Ci;
-    const double gj = dpoly(ar, hj) * (rj.c5 * PrRho_j);
+    const double gj = dpoly_from(t1j, ar, rj.h, 1.5, 0.5) * (rj.c5 * PrRho_j);
     const double v_ij = o.v - vj;
     const double dot = v_ij * (dir * ar);
     // artificial viscosity (calculators.cpp:148-172): alpha = 1, beta = 2, eta^2 = 0.01 hbar^2
     double visc_ac = 0.0, visc_ec = 0.0;
     if (!(dot > 0)) {
-        const double mu = (hb * dot) * iD;
+        const double mu = ((0.5 * hs) * dot) * iD;
         const double two_mu2 = 2.0 * (mu * mu);
         const double irho = 2.0 * irs;               // 1 / ((rho_i + rho_j) / 2)
         visc_ac = fma(-o.c_ac, mu, two_mu2) * irho;
         visc_ec = fma(-o.c_ec, mu, two_mu2) * irho;
     }
-    const double ta = fma(gb, visc_ac, gi + gj);
+    const double ta = fma(gb, visc_ac, gj);
     const double te = (v_ij * gb) * fma(0.5, visc_ec, o.PrRho);
     if (UM) { accA += ta; accE += te; }
     else { accA = fma(mj, ta, accA); accE = fma(mj, te, accE); }
@@ -457,8 +468,9 @@ __device__ __forceinline__ bool pair_terms(const Own<ADIA> &o, double ar, double
 // Shared-memory image of a tile and its surroundings for the force pass.
 struct ForceSmem {
     double x[kTile + 2 * kFHalo + 2];
-    Rec rA[kTile + 2 * kFHalo];
-    Rec rB[kTile + 2 * kFHalo];
+    // records split in 16-byte halves so that a warp's LDS.128 is conflict-free; [0] = new state A, [1] = old state B
+    double2 hc[2][kTile + 2 * kFHalo];   // (h, c5)
+    double2 rk[2][kTile + 2 * kFHalo];   // (rho, kap)
     double vA[kTile + 2 * kFHalo], uA[kTile + 2 * kFHalo];
     double vB[kTile + 2 * kFHalo], uB[kTile + 2 * kFHalo];
     unsigned idx[kTile + 2 * kFHalo];
@@ -491,7 +503,10 @@ __device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &
         const double ar = DIR > 0 ? (sx[k] - o.x) : (o.x - sx[k]);
         if (!(ar < reach)) break;                 // also the +-INF sentinels
         const bool useA = sees_new_state<SEL>(S.idx[k], o.idx);
-        const Rec rj = useA ? S.rA[k] : S.rB[k];
+        const int sel = useA ? 0 : 1;
+        const double2 hc = S.hc[sel][k], rk = S.rk[sel][k];
+        Rec rj;
+        rj.h = hc.x; rj.c5 = hc.y; rj.rho = rk.x; rj.kap = rk.y;
         const double vj = (useA && !FIRST) ? S.vA[k] : S.vB[k];
         const double uj = (useA && !FIRST) ? S.uA[k] : S.uB[k];
         const double mj = UM ? 0.0 : __ldg(A.F.m + wbase + k);
@@ -507,7 +522,7 @@ __device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &
             const double ar = DIR > 0 ? (xj - o.x) : (o.x - xj);
             if (!(ar < reach)) break;
             const bool useA = sees_new_state<SEL>(__ldg(A.F.idx + j), o.idx);
-            const Rec rj = useA ? A.F.recA[j] : A.F.recB[j];
+            const Rec rj = useA ? A.F.rec[j].A : A.F.rec[j].B;
             const double vj = (useA && !FIRST) ? ldv<true>(A.F.vA + j) : __ldg(A.F.vB + j);
             const double uj = (useA && !FIRST) ? ldv<true>(A.F.uA + j) : __ldg(A.F.uB + j);
             const double mj = UM ? 0.0 : __ldg(A.F.m + j);
@@ -536,10 +551,13 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
         const int j = wbase + k;
         sx[k] = A.F.x[j];
         S.idx[k] = A.F.idx[j];
-        S.rB[k] = A.F.recB[j];
+        {
+            const Rec2 r2 = A.F.rec[j];
+            S.hc[0][k] = make_double2(r2.A.h, r2.A.c5); S.rk[0][k] = make_double2(r2.A.rho, r2.A.kap);
+            S.hc[1][k] = make_double2(r2.B.h, r2.B.c5); S.rk[1][k] = make_double2(r2.B.rho, r2.B.kap);
+        }
         S.vB[k] = __ldg(A.F.vB + j);
         S.uB[k] = __ldg(A.F.uB + j);
-        S.rA[k] = A.F.recA[j];
         if (!FIRST) { S.vA[k] = ldv<true>(A.F.vA + j); S.uA[k] = ldv<true>(A.F.uA + j); }
     }
     if (threadIdx.x == 0) { sx[-1] = -INFINITY; sx[wn] = INFINITY; }
@@ -552,7 +570,11 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
         const int ks = s - wbase;
         Own<ADIA> o;
         const double vi = A.vh[s], ui = A.uh[s];
-        o.set(sx[ks], S.idx[ks], S.rA[ks], vi, ui, A.Pstale[s]);
+        {
+            Rec ro;
+            ro.h = S.hc[0][ks].x; ro.c5 = S.hc[0][ks].y; ro.rho = S.rk[0][ks].x; ro.kap = S.rk[0][ks].y;
+            o.set(sx[ks], S.idx[ks], ro, vi, ui, A.Pstale[s]);
+        }
         const double reach = kRadius * Hb;
         double a_sum = 0.0, e_sum = 0.0;
         int jmin = s, jmax = s;
@@ -560,6 +582,7 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
         force_side<SEL, ADIA, UM, FIRST, -1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmin);
         force_side<SEL, ADIA, UM, FIRST, +1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmax);
         if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
+        a_sum = fma(-o.PrRho, A.F.gsum[s], a_sum);        // - P_i/(rho_i^2 om_i) sum_j m_j gradW_ij(h_i)
         if (!A.kick) {
             A.a[s] = a_sum;
             A.du[s] = e_sum;
@@ -604,7 +627,7 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
 // First force sweep of a step over every alive particle (also the only one for the
 // jacobi order and for the kick-less t = 0 pass).
 template <int SEL, bool ADIA, bool UM>
-__global__ void __launch_bounds__(kTile) k_force_first(SweepArgs A) {
+__global__ void __launch_bounds__(kTile, 4) k_force_first(SweepArgs A) {
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
     const double Hb = __longlong_as_double((long long)ctl->hmax_bits);

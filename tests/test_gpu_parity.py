@@ -55,7 +55,8 @@ def _compare_ghosts(f, ref, na, what, t0):
         cols += ["acc", "du_dt"]
     for c in cols:
         e = scaled_err(f[na:, COLS[c]], ref[na:, COLS[c]])
-        assert e < TOL, "%s: ghost %s differs by %.3e" % (what, c, e)
+        lim = TOL if c not in ("acc", "du_dt") else 1e-9      # copies of the alive values: same limits
+        assert e < lim, "%s: ghost %s differs by %.3e" % (what, c, e)
 
 
 def test_device_is_b200_class():
