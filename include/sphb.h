@@ -94,7 +94,8 @@ enum {
     SPHB_ERR_NO_BRACKET = 9,       /* GSL bisection "endpoints do not straddle" (aborts) */
     SPHB_ERR_NOT_CONVERGED = 10,   /* ordered sweep did not reach its fixed point in max_sweeps */
     SPHB_ERR_UNSORTED = 11,        /* internal: order invariant violated */
-    SPHB_ERR_NO_DEVICE = 12        /* no CUDA device / extension unusable: there is NO CPU fallback */
+    SPHB_ERR_NO_DEVICE = 12,       /* no CUDA device / extension unusable: there is NO CPU fallback */
+    SPHB_ERR_HALO = 13             /* x-slab run: the halo is thinner than the kernel support reaches */
 };
 
 typedef struct sphb_handle sphb_handle;
@@ -159,6 +160,37 @@ enum { SPHB_PHASES = 6 };
 int sphb_set_profiling(sphb_handle *h, int on);
 /* ms[p], launches[p] accumulated since the last reset; reset != 0 clears them */
 int sphb_get_phase_times(sphb_handle *h, double *ms, long long *launches, int reset);
+
+/* ---- x-slab decomposition across GPUs -------------------------------------------------------
+ * No counterpart in the reference (it is single-threaded); these entry points run
+ * SPHSimulation::step_forward (sph_simulation.cpp:55-108) and init_particles (setup.cpp:143-228)
+ * phase by phase on ONE slab of an x-sorted decomposition, so that the caller can exchange halo
+ * messages with the neighbouring ranks between the phases.  One handle per rank.  The library packs
+ * and unpacks messages in caller-owned DEVICE buffers of sphb_slab_message_doubles() doubles; moving
+ * them (NCCL send/recv, or a device copy) is the caller's job.  side: -1 = left neighbour, +1 = right.
+ * Step: step_begin | exchange BASE | density | exchange RECORDS | force_first, refine |
+ *       { exchange ITERATE | refine } until no rank reports halo_changed | step_end.               */
+enum { SPHB_MSG_BASE = 0, SPHB_MSG_RECORDS = 1, SPHB_MSG_ITERATE = 2 };
+/* this handle holds global particle indices [index_offset, index_offset + n_alive) of n_global;
+ * halo_count particles travel per edge (must exceed the kernel reach in particles; too thin a halo is
+ * detected on the device and reported as SPHB_ERR_HALO) */
+int sphb_slab_configure(sphb_handle *h, int rank, int world, int halo_count, long long index_offset,
+                        long long n_global);
+int sphb_slab_message_doubles(const sphb_handle *h, int what);
+int sphb_slab_pack(sphb_handle *h, int what, int side, double *d_buf);
+int sphb_slab_unpack(sphb_handle *h, int what, int side, const double *d_buf);
+int sphb_slab_step_begin(sphb_handle *h);   /* kick-drift, order check (+ sort), wall ghosts */
+int sphb_slab_density(sphb_handle *h);      /* density + root-find + omega + records of own particles */
+int sphb_slab_force_first(sphb_handle *h);  /* first force sweep + second kick */
+int sphb_slab_refine(sphb_handle *h);       /* ordered-sweep refinement until the local work list is empty */
+int sphb_slab_poll(sphb_handle *h, int *halo_changed);   /* did the last ITERATE unpack change anything here? */
+int sphb_slab_step_end(sphb_handle *h);
+/* t = 0 in phases: init_lattice | [adiabatic: exchange BASE | sphb_density(h,0) | prepass] | sphb_ghosts |
+ * exchange BASE | sphb_density(h,1) | records | exchange RECORDS | forces */
+int sphb_slab_init_lattice(sphb_handle *h);
+int sphb_slab_prepass(sphb_handle *h);
+int sphb_slab_records(sphb_handle *h);
+int sphb_slab_forces(sphb_handle *h);
 
 /* No counterpart in the reference.  The same density / root-find / omega pass as sphb_density,
  * for callers that cannot allocate device memory when they need it (the whole device already

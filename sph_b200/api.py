@@ -140,6 +140,14 @@ def load_library():
     L.sphb_get_config.argtypes = [p, C.POINTER(SphbConfig)]
     L.sphb_set_profiling.argtypes = [p, i]
     L.sphb_get_phase_times.argtypes = [p, C.POINTER(d), C.POINTER(C.c_longlong), i]
+    ll = C.c_longlong
+    L.sphb_slab_configure.argtypes = [p, i, i, i, ll, ll]
+    L.sphb_slab_message_doubles.argtypes = [p, i]
+    L.sphb_slab_pack.argtypes = [p, i, i, p]
+    L.sphb_slab_unpack.argtypes = [p, i, i, p]
+    for name in ('step_begin', 'density', 'force_first', 'refine', 'step_end', 'init_lattice', 'prepass', 'records', 'forces'):
+        getattr(L, 'sphb_slab_' + name).argtypes = [p]
+    L.sphb_slab_poll.argtypes = [p, ip]
     L.sphb_density_static.argtypes = [p, p, p, i, d, d, d, i, p, p, p]
     L.sphb_build_arch.argtypes = []
     L.sphb_build_arch.restype = C.c_char_p

@@ -50,6 +50,10 @@ struct sphb_handle {
     size_t aos_cap = 0;
     int *d_newton = nullptr, *d_nbr = nullptr;  // index-ordered count outputs (lazy)
     bool ghost_in_half = false;   // ghosts' v,u live in the pads of vh/uh (after a step)
+    // x-slab decomposition (sphb_slab_*): this handle owns global indices [idx_base, idx_base + na)
+    bool slab = false, halo_l = false, halo_r = false;
+    int rank = 0, world = 1, K = 0;
+    long long idx_base = 0, n_global = 0;
     bool uniform_mass = true;
     double m0 = 0.0;
     bool have_counts = false;
@@ -99,6 +103,7 @@ const char *err_text(int code) {
         case SPHB_ERR_NO_BRACKET: return "bisection: endpoints do not straddle y=0";
         case SPHB_ERR_NOT_CONVERGED: return "ordered sweep did not converge within max_sweeps";
         case SPHB_ERR_UNSORTED: return "x-order invariant violated";
+        case SPHB_ERR_HALO: return "x-slab halo thinner than the kernel support (raise halo_count)";
         default: return "error";
     }
 }
@@ -125,6 +130,11 @@ int read_ctl(sphb_handle *H) {
         return code;
     }
     return SPHB_OK;
+}
+
+// ghosts made at the walls (pads that hold a neighbouring slab's particles do not count)
+int wall_ghosts(const sphb_handle *H) {
+    return (H->halo_l ? 0 : H->h_ctl->GL) + (H->halo_r ? 0 : H->h_ctl->GR);
 }
 
 void phase_begin(sphb_handle *H) {
@@ -296,8 +306,9 @@ SweepArgs sweep_args(sphb_handle *H) {
     return A;
 }
 
-// SPHSimulation::step_forward (sph_simulation.cpp:55-108), once.
-int step_once(sphb_handle *H) {
+// SPHSimulation::step_forward (sph_simulation.cpp:55-108) in four phases; between them an x-slab
+// run exchanges halos with its neighbours (sphb_slab_*), a single-GPU run just goes on.
+int step_begin(sphb_handle *H) {   // kick-drift, order check (+ sort), wall ghosts
     if (H->epoch > 0x7fff0000 - 2 * H->opt.max_sweeps) {   // stamp wrap-around
         CK(cudaMemsetAsync(H->dirty, 0, sizeof(int) * (size_t)nblk(H->cap_alive, kTile), H->stream));
         H->epoch = 8;
@@ -308,9 +319,6 @@ int step_once(sphb_handle *H) {
     phase_end(H, 0);
     // the order check decides on the host whether the radix sort runs
     TRY(read_ctl(H));
-    if (H->steps > 0) {           // the previous step's sweep count is in the block just read
-        // (accounted in sphb_step after the final read as well)
-    }
     if (H->h_ctl->unsorted || H->opt.sort_every_step) {
         TRY(sort_alive(H, false));
         TRY(launch_begin(H, 1));
@@ -320,24 +328,42 @@ int step_once(sphb_handle *H) {
     TRY(launch_ghost_build(H, 1, 0, H->vh, H->uh, H->vh, H->uh));
     H->ghost_in_half = true;
     phase_end(H, 2);
+    return SPHB_OK;
+}
+
+int step_density(sphb_handle *H) {
     TRY(launch_density(H, 1, 0, 1, H->Pn));
     phase_end(H, 3);
+    return SPHB_OK;
+}
 
+SweepArgs step_sweep_args(sphb_handle *H) {
     SweepArgs A = sweep_args(H);
     A.Pstale = H->P; A.Pout = H->Pn;
     A.vh = H->vh; A.uh = H->uh;
     A.F.vA = H->vh; A.F.uA = H->uh;
     A.F.vB = H->vh; A.F.uB = H->uh;
-    if (H->opt.order == SPHB_ORDER_JACOBI) {
-        TRY(launch_first_sel<SEL_ALIVE>(H, A));
-        phase_end(H, 4);
-    } else {
-        TRY(launch_first_sel<SEL_INDEX>(H, A));
-        phase_end(H, 4);
-        A.F.vA = H->vn; A.F.uA = H->un;   // from now on lower-index neighbours are seen fully kicked
-        TRY(launch_refine(H, A));
-        phase_end(H, 5);
-    }
+    return A;
+}
+
+int step_force_first(sphb_handle *H) {
+    SweepArgs A = step_sweep_args(H);
+    if (H->opt.order == SPHB_ORDER_JACOBI) TRY(launch_first_sel<SEL_ALIVE>(H, A));
+    else TRY(launch_first_sel<SEL_INDEX>(H, A));
+    phase_end(H, 4);
+    return SPHB_OK;
+}
+
+int step_refine(sphb_handle *H) {   // runs until this handle's work list is empty
+    if (H->opt.order == SPHB_ORDER_JACOBI) return SPHB_OK;
+    SweepArgs A = step_sweep_args(H);
+    A.F.vA = H->vn; A.F.uA = H->un;   // lower-index neighbours are seen fully kicked
+    TRY(launch_refine(H, A));
+    phase_end(H, 5);
+    return SPHB_OK;
+}
+
+int step_finish(sphb_handle *H) {
     H->epoch += H->opt.max_sweeps + 2;
     std::swap(H->v, H->vn);
     std::swap(H->u, H->un);
@@ -346,6 +372,14 @@ int step_once(sphb_handle *H) {
     std::swap(H->P, H->Pn);
     H->steps++;
     return SPHB_OK;
+}
+
+int step_once(sphb_handle *H) {
+    TRY(step_begin(H));
+    TRY(step_density(H));
+    TRY(step_force_first(H));
+    TRY(step_refine(H));
+    return step_finish(H);
 }
 
 int ensure_aos(sphb_handle *H, size_t n) {
@@ -370,6 +404,7 @@ PackArgs pack_args(sphb_handle *H) {
     A.gorder = H->gorder; A.cnt = H->cnt; A.aos = H->d_aos;
     A.out_newton = nullptr; A.out_nbr = nullptr;
     A.ctl = H->d_ctl; A.pad = H->pad; A.na = H->na; A.ng = 0;
+    A.idx_base = (unsigned)H->idx_base;
     return A;
 }
 
@@ -385,10 +420,11 @@ int ghosts_to_current(sphb_handle *H) {
 
 int pack_to_staging(sphb_handle *H, bool with_counts, int *n_total) {
     TRY(read_ctl(H));
-    const int ng = H->h_ctl->GL + H->h_ctl->GR;
+    const int ng = wall_ghosts(H);
     const int n = H->na + ng;
     TRY(ensure_aos(H, (size_t)n));
     PackArgs A = pack_args(H);
+    A.ng = ng;
     if (with_counts) {
         if (!H->d_newton) {
             TRY(dalloc(H, &H->d_newton, (size_t)H->cap_alive + 2 * H->pad));
@@ -405,6 +441,23 @@ int pack_to_staging(sphb_handle *H, bool with_counts, int *n_total) {
     return SPHB_OK;
 }
 
+}  // namespace
+
+namespace {
+SlabArgs slab_args(sphb_handle *H, int side) {
+    SlabArgs A;
+    A.x = H->x; A.m = H->m; A.vh = H->vh; A.uh = H->uh; A.vn = H->vn; A.un = H->un;
+    A.h = H->h; A.rho = H->rho; A.P = H->P; A.idx = H->idx; A.rec = H->rec;
+    A.dirty = H->dirty; A.wl[0] = H->wl0; A.wl[1] = H->wl1; A.ctl = H->d_ctl;
+    A.pad = H->pad; A.na = H->na; A.K = H->K; A.side = side;
+    return A;
+}
+int slab_flags(sphb_handle *H) {
+    k_slab_flags<<<1, 1, 0, H->stream>>>(H->d_ctl, H->halo_l ? 1 : 0, H->halo_r ? 1 : 0);
+    H->launches++;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
 }  // namespace
 
 extern "C" {
@@ -645,7 +698,7 @@ int sphb_ghosts(sphb_handle *H, int *n_ghost) {
     TRY(launch_ghost_build(H, 1, 0, H->v, H->u, H->v, H->u));
     H->ghost_in_half = false;
     TRY(read_ctl(H));
-    const int ng = H->h_ctl->GL + H->h_ctl->GR;
+    const int ng = wall_ghosts(H);
     H->cfg.n_ghost = ng;
     H->cfg.n_part = H->na + ng;
     if (n_ghost) *n_ghost = ng;
@@ -664,13 +717,19 @@ int sphb_density(sphb_handle *H, int include_ghosts) {
     return read_ctl(H);
 }
 
-int sphb_forces(sphb_handle *H) {
+// records (omega, 1/h^5, ...) of every particle for its stored h, density — first half of sphb_forces
+int sphb_slab_records(sphb_handle *H) {
     if (!H) return SPHB_ERR_INVALID;
     CK(cudaSetDevice(H->device));
     TRY(ghosts_to_current(H));
     TRY(launch_begin(H, 0));
     // omega of every particle for its stored h, density (calc_omega), nothing else changes
-    TRY(launch_density(H, 0, 0, 0, H->P));
+    return launch_density(H, 0, 0, 0, H->P);
+}
+// second half of sphb_forces: the order-independent acceleration / du_dt pass, no kick
+int sphb_slab_forces(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
     SweepArgs A = sweep_args(H);
     A.kick = 0;
     A.Pstale = H->P; A.Pout = H->P;
@@ -681,6 +740,12 @@ int sphb_forces(sphb_handle *H) {
     return read_ctl(H);
 }
 
+int sphb_forces(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    TRY(sphb_slab_records(H));
+    return sphb_slab_forces(H);
+}
+
 int sphb_omega(sphb_handle *H, double *omega, int cap) {
     if (!H || !omega) return SPHB_ERR_INVALID;
     CK(cudaSetDevice(H->device));
@@ -688,9 +753,10 @@ int sphb_omega(sphb_handle *H, double *omega, int cap) {
     TRY(launch_begin(H, 0));
     TRY(launch_density(H, 0, 0, 0, H->P, true));   // omega only: h, density stay as stored
     TRY(read_ctl(H));
-    const int n = H->na + H->h_ctl->GL + H->h_ctl->GR;
+    const int n = H->na + wall_ghosts(H);
     if (n > cap) { H->err = "download buffer too small"; return SPHB_ERR_CAPACITY; }
-    k_pack_f64<<<nblk(n, 256), 256, 0, H->stream>>>(H->omn, H->tmp, H->idx, H->gorder, H->d_ctl, H->pad, H->na);
+    k_pack_f64<<<nblk(n, 256), 256, 0, H->stream>>>(H->omn, H->tmp, H->idx, H->gorder, H->d_ctl, H->pad, H->na,
+                                                    n - H->na, (unsigned)H->idx_base);
     H->launches++;
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(omega, H->tmp, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, H->stream));
@@ -711,15 +777,17 @@ int sphb_step(sphb_handle *H, int nsteps) {
         H->sweeps_last = used;
         H->sweeps_total += used;
     }
-    H->cfg.n_ghost = H->h_ctl->GL + H->h_ctl->GR;
+    H->cfg.n_ghost = wall_ghosts(H);
     H->cfg.n_part = H->na + H->cfg.n_ghost;
     return SPHB_OK;
 }
 
-int sphb_init_lattice(sphb_handle *H) {
+// lattice of setup.cpp:145-185 for this handle's particles (all of them, or global indices
+// [idx_base, idx_base + na) of an x-slab run); no ghosts, no densities yet
+int sphb_slab_init_lattice(sphb_handle *H) {
     if (!H) return SPHB_ERR_INVALID;
     CK(cudaSetDevice(H->device));
-    const int n = H->na;
+    const long long n = H->slab ? H->n_global : (long long)H->na;
     if (n < 2) { H->err = "need at least 2 particles"; return SPHB_ERR_INVALID; }
     // setup.cpp:145-153,158-159, same operations in the same order
     double max_x = H->cfg.limit;
@@ -730,28 +798,138 @@ int sphb_init_lattice(sphb_handle *H) {
     const double spacing2 = (max_x - min_x) / (n - 1);
     LatticeArgs L;
     L.x = H->x; L.v = H->v; L.u = H->u; L.a = H->a; L.du = H->du; L.h = H->h; L.rho = H->rho; L.P = H->P; L.m = H->m;
-    L.idx = H->idx; L.slot_id = H->slot_id; L.pad = H->pad; L.na = n;
+    L.idx = H->idx; L.slot_id = H->slot_id; L.pad = H->pad; L.na = H->na; L.i0 = H->slab ? H->idx_base : 0;
     L.min_x = min_x; L.spacing = spacing2; L.v0 = H->cfg.v_0;
     L.u0 = (H->cfg.pressure_calc == SPHB_ADIABATIC) ? 1 / (kGamma - 1) : 0.0;
     L.h0 = H->opt.variable_h ? H->cfg.h_factor * spacing2 : H->opt.fixed_h;
     L.mass = H->cfg.mass;
     H->uniform_mass = true;
     H->m0 = H->cfg.mass;
-    k_lattice<<<nblk(n, 256), 256, 0, H->stream>>>(L);
+    k_lattice<<<nblk(H->na, 256), 256, 0, H->stream>>>(L);
     H->launches++;
     CK(cudaGetLastError());
     CK(cudaMemsetAsync(H->d_ctl, 0, sizeof(Ctl), H->stream));   // no ghosts yet
     H->ghost_in_half = false;
+    return slab_flags(H);
+}
+
+// v_i = +-c_s from the pre-pass density (setup.cpp:197-201)
+int sphb_slab_prepass(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    k_prepass<<<nblk(H->na, 256), 256, 0, H->stream>>>(H->x, H->v, H->u, H->rho, H->P, H->pad, H->na);
+    H->launches++;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
+int sphb_init_lattice(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    if (H->slab) { H->err = "x-slab runs initialise phase by phase (sphb_slab_*), with halo exchanges in between"; return SPHB_ERR_INVALID; }
+    TRY(sphb_slab_init_lattice(H));
     if (H->cfg.pressure_calc == SPHB_ADIABATIC) {
         // pre-pass, setup.cpp:192-202
         TRY(sphb_density(H, 0));
-        k_prepass<<<nblk(n, 256), 256, 0, H->stream>>>(H->x, H->v, H->u, H->rho, H->P, H->pad, n);
-        H->launches++;
-        CK(cudaGetLastError());
+        TRY(sphb_slab_prepass(H));
     }
     TRY(sphb_ghosts(H, nullptr));
     TRY(sphb_density(H, 1));
     return sphb_forces(H);
+}
+
+// ------------------------------------------------------------------------------------
+// x-slab decomposition across the GPUs of a node.  The library does the
+// device work of every phase and packs / unpacks halo messages in caller-owned device
+// buffers; moving the messages between ranks (NCCL send/recv, or a device copy when the
+// ranks share a process) is the caller's part — sph_b200/slabs.py.
+
+int sphb_slab_configure(sphb_handle *H, int rank, int world, int halo_count, long long index_offset,
+                        long long n_global) {
+    if (!H) return SPHB_ERR_INVALID;
+    if (world < 1 || rank < 0 || rank >= world || halo_count < 1 || halo_count > H->pad || index_offset < 0 ||
+        n_global < H->na || index_offset + H->na > n_global || n_global >= (1ll << 31)) {
+        H->err = "bad slab configuration (halo_count must fit pad_capacity; global indices must fit 31 bits)";
+        return SPHB_ERR_INVALID;
+    }
+    CK(cudaSetDevice(H->device));
+    H->slab = world > 1;
+    H->rank = rank; H->world = world; H->K = halo_count;
+    H->idx_base = index_offset; H->n_global = n_global;
+    H->halo_l = rank > 0;
+    H->halo_r = rank < world - 1;
+    return slab_flags(H);
+}
+
+int sphb_slab_message_doubles(const sphb_handle *H, int what) {
+    if (!H || what < 0 || what > 2 || H->K < 1) return -1;
+    return msg_rows(what) * H->K + 8;
+}
+
+int sphb_slab_pack(sphb_handle *H, int what, int side, double *d_buf) {
+    if (!H || !d_buf || what < 0 || what > 2 || (side != -1 && side != 1)) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    SlabArgs A = slab_args(H, side);
+    if (what == MSG_BASE && !H->ghost_in_half) { A.vh = H->v; A.uh = H->u; }   // t = 0: the current v, u
+    k_slab_pack<<<std::max(1, std::min(nblk(H->K, 256), 64)), 256, 0, H->stream>>>(A, what, d_buf);
+    H->launches++;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
+int sphb_slab_unpack(sphb_handle *H, int what, int side, const double *d_buf) {
+    if (!H || !d_buf || what < 0 || what > 2 || (side != -1 && side != 1)) return SPHB_ERR_INVALID;
+    if ((side < 0 && !H->halo_l) || (side > 0 && !H->halo_r)) { H->err = "no neighbouring slab on that side"; return SPHB_ERR_INVALID; }
+    CK(cudaSetDevice(H->device));
+    SlabArgs A = slab_args(H, side);
+    if (what == MSG_BASE && !H->ghost_in_half) { A.vh = H->v; A.uh = H->u; }
+    k_slab_unpack<<<1, 1024, 0, H->stream>>>(A, what, d_buf);
+    H->launches++;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
+int sphb_slab_step_begin(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    return step_begin(H);
+}
+int sphb_slab_density(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    return step_density(H);
+}
+int sphb_slab_force_first(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    return step_force_first(H);
+}
+int sphb_slab_refine(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    return step_refine(H);
+}
+// 1 in *halo_changed: an ITERATE message unpacked since the last call differed from the copy held
+// here, i.e. this rank queued tiles again and the sweep is not known to be finished.
+int sphb_slab_poll(sphb_handle *H, int *halo_changed) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    TRY(read_ctl(H));
+    if (halo_changed) *halo_changed = H->h_ctl->halo_changed;
+    CK(cudaMemsetAsync(&H->d_ctl->halo_changed, 0, sizeof(int), H->stream));
+    return SPHB_OK;
+}
+int sphb_slab_step_end(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    TRY(step_finish(H));
+    TRY(read_ctl(H));
+    phase_collect(H);
+    const int used = (H->opt.order == SPHB_ORDER_JACOBI) ? 1 : H->h_ctl->sweeps_used;
+    H->sweeps_last = used;
+    H->sweeps_total += used;
+    H->cfg.n_ghost = wall_ghosts(H);
+    H->cfg.n_part = H->na + H->cfg.n_ghost;
+    return SPHB_OK;
 }
 
 int sphb_get_counters(sphb_handle *H, sphb_counters *out) {
@@ -760,7 +938,7 @@ int sphb_get_counters(sphb_handle *H, sphb_counters *out) {
     memset(out, 0, sizeof *out);
     TRY(read_ctl(H));
     out->n_alive = H->na;
-    out->n_ghost = H->h_ctl->GL + H->h_ctl->GR;
+    out->n_ghost = wall_ghosts(H);
     out->steps = H->steps;
     out->sweeps_total = H->sweeps_total;
     out->sweeps_last = H->sweeps_last;

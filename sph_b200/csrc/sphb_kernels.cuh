@@ -39,7 +39,7 @@ constexpr int kTile = 256;             // particles per CTA tile
 enum ErrCode {
     E_OK = 0, E_CAPACITY = 3, E_NEGATIVE_H = 4, E_LOW_DENSITY = 5, E_GHOST_ZERO_H = 6,
     E_ZERO_DERIVATIVE = 7, E_NOT_FINITE = 8, E_NO_BRACKET = 9, E_NOT_CONVERGED = 10,
-    E_UNSORTED = 11
+    E_UNSORTED = 11, E_HALO = 13
 };
 
 // Device control block (one per handle), read back by the host at sync points.
@@ -52,7 +52,9 @@ struct Ctl {
     unsigned long long fallbacks;  // bisection fallbacks taken
     int nwork[2];                  // tiles in the work list of the sweep with even / odd stamp
     int sweeps_used;               // force sweeps the last step needed
-    int pad_;
+    int epoch_cur;                 // stamp of the most recent force sweep (handed from launch to launch)
+    int halo_left, halo_right;     // the pad on that side holds another slab's particles, not wall ghosts
+    int halo_changed;              // an incoming halo iterate differed from the copy held here
     unsigned long long force_pairs; // (i,j) pairs evaluated by the first force sweep (self included)
 };
 
@@ -145,7 +147,7 @@ __device__ __forceinline__ void density_term(double r, double a1, double a2, dou
 
 // one side (DIR = -1 left, +1 right) of the scan around sorted slot s
 template <bool UM, int DIR>
-__device__ __forceinline__ void density_side(const double *sx, int wbase, int wn, const double *__restrict__ gx,
+__device__ __forceinline__ void density_side(Ctl *ctl, bool own, const double *sx, int wbase, int wn, const double *__restrict__ gx,
                                              const double *__restrict__ m, int s, int lo, int hi, double xi,
                                              double h, double a1, double a2, double a3, double r_in, double &sw,
                                              double &sg, double &sgr, int &c) {
@@ -169,8 +171,9 @@ __device__ __forceinline__ void density_side(const double *sx, int wbase, int wn
         r = DIR > 0 ? (sx[k] - xi) : (xi - sx[k]);
     }
     // rare: the scan ran off the staged part (more than kDHalo neighbours on this side)
+    int j = wbase + k;
 #pragma unroll 1
-    for (int j = wbase + k; j >= lo && j < hi; j += DIR) {
+    for (; j >= lo && j < hi; j += DIR) {
         r = DIR > 0 ? (__ldg(gx + j) - xi) : (xi - __ldg(gx + j));
         if (r < r_in) {
             c++;
@@ -181,10 +184,13 @@ __device__ __forceinline__ void density_side(const double *sx, int wbase, int wn
             return;
         }
     }
+    // every particle on this side lies inside the support: fine next to a wall, but on a slab
+    // edge it means the halo is thinner than the kernel reaches
+    if (own && (DIR < 0 ? ctl->halo_left : ctl->halo_right)) raise(ctl, E_HALO, s);
 }
 
 template <bool UM>
-__device__ __forceinline__ void density_sums(const double *sx, int wbase, int wn, const double *__restrict__ gx,
+__device__ __forceinline__ void density_sums(Ctl *ctl, bool own, const double *sx, int wbase, int wn, const double *__restrict__ gx,
                                              const double *__restrict__ m, int s, int lo, int hi, double xi,
                                              double h, double &Sw, double &Sg, double &Sgr, int &cnt) {
     const double a1 = 2.5 * h, a2 = 1.5 * h, a3 = 0.5 * h;
@@ -194,8 +200,8 @@ __device__ __forceinline__ void density_sums(const double *sx, int wbase, int wn
     double sw = self, sg = UM ? self : self * __ldg(m + s);
     int c = 1;
     double grl = 0.0, grr = 0.0;
-    density_side<UM, -1>(sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, grl, c);
-    density_side<UM, +1>(sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, grr, c);
+    density_side<UM, -1>(ctl, own, sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, grl, c);
+    density_side<UM, +1>(ctl, own, sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, grr, c);
     Sw = sw;
     Sg = sg;
     Sgr = grl - grr;                              // gradW carries sign(x_i - x_j): + for left neighbours
@@ -241,7 +247,9 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
 
     const int s = t0 + threadIdx.x;
     double hloc = 0.0;
-    if (s >= lo && s < hi) {
+    // pad slots that hold another slab's particles get everything from their owner
+    const bool halo_slot = (s < A.pad && ctl->halo_left) || (s >= A.pad + A.na && ctl->halo_right);
+    if (s >= lo && s < hi && !halo_slot) {
         const bool is_pad = (s < A.pad) || (s >= A.pad + A.na);
         const bool do_root = VARH && (is_pad ? A.root_ghosts : A.root_alive);
         const double xi = sx[s - wbase];
@@ -254,7 +262,7 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
         double Sw, Sg, Sgr = 0.0;
 #define SPHB_EVAL(H_, F_, DF_, DSUM_)                                                           \
     {                                                                                           \
-        density_sums<UM>(sx, wbase, wn, A.x, A.m, s, lo, hi, xi, (H_), Sw, Sg, Sgr, cnt);       \
+        density_sums<UM>(ctl, !is_pad, sx, wbase, wn, A.x, A.m, s, lo, hi, xi, (H_), Sw, Sg, Sgr, cnt); \
         const double ih_ = 1.0 / (H_), ih2_ = ih_ * ih_, ih4_ = ih2_ * ih2_;                    \
         const double rho_ = mi * (kSigma * (Sw * (ih4_ * ih_)));                                \
         F_ = rho_ - mi * A.hfac * ih_;                                                          \
@@ -284,6 +292,8 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
                 }
                 if (cont && ctl->err_code == 0) {
                     // bisection fallback on [1e-8, 2 limit], gsl_root_test_interval rel 1e-4
+                    // (its bracket end 2*limit sums over the whole domain: a slab cannot evaluate it)
+                    if (ctl->halo_left | ctl->halo_right) raise(ctl, E_HALO, s);
                     atomicAdd(&ctl->fallbacks, 1ull);
                     double xl = kEps, xh = 2 * A.limit, fl, fh, dfx, dsx;
                     int c2 = cnt;
@@ -529,6 +539,7 @@ __device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &
             if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
         }
     }
+    if ((j < lo || j >= hi) && (DIR < 0 ? A.ctl->halo_left : A.ctl->halo_right)) raise(A.ctl, E_HALO, wbase + ks);
     jend = j - DIR;
     a_sum = DIR > 0 ? (a_sum + accA) : (a_sum - accA);
     e_sum = DIR > 0 ? (e_sum - accE) : (e_sum + accE);
@@ -601,10 +612,10 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
                 const double vo = __ldcg(A.vn + s), uo = __ldcg(A.un + s);
                 changed = (__double_as_longlong(vf) != __double_as_longlong(vo)) ||
                           (__double_as_longlong(uf) != __double_as_longlong(uo));
-                if (changed) {
-                    A.a[s] = a_sum; A.du[s] = e_sum;
-                    __stcg(A.vn + s, vf); __stcg(A.un + s, uf);
-                }
+                // a, du feed the next step's first kick: they must come from THIS (possibly final)
+                // evaluation even when the kicked values round to what is already stored
+                A.a[s] = a_sum; A.du[s] = e_sum;
+                if (changed) { __stcg(A.vn + s, vf); __stcg(A.un + s, uf); }
             }
             if (changed && SEL == SEL_INDEX) {
                 // every tile holding a particle within reach must be looked at again next sweep
@@ -633,6 +644,7 @@ __global__ void __launch_bounds__(kTile, 4) k_force_first(SweepArgs A) {
     const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
     bool changed;
     int npairs;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->epoch_cur = A.epoch; ctl->sweeps_used = 1; }
     force_tile<SEL, ADIA, UM, true>(A, blockIdx.x, lo, hi, Hb, A.epoch, changed, npairs);
     // pair statistics for the roofline accounting (one atomic per warp)
     for (int o = 16; o > 0; o >>= 1) npairs += __shfl_xor_sync(0xffffffffu, npairs, o);
@@ -654,8 +666,9 @@ __global__ void __launch_bounds__(kTile) k_force_refine(SweepArgs A, int max_swe
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
     const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
-    int epoch = A.epoch;          // stamp of the first sweep (k_force_first), which filled wl[(epoch + 1) & 1]
-    int used = 1;
+    int epoch = ctl->epoch_cur;   // stamp of the latest sweep, which filled wl[(epoch + 1) & 1]
+    int used = ctl->sweeps_used;
+    grid.sync();                  // everybody has read the hand-over words before block 0 rewrites them
     while (true) {
         const int cur = (epoch + 1) & 1;
         const int nwork = *((volatile int *)&ctl->nwork[cur]);
@@ -676,7 +689,7 @@ __global__ void __launch_bounds__(kTile) k_force_refine(SweepArgs A, int max_swe
         }
         grid.sync();
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) ctl->sweeps_used = used;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->sweeps_used = used; ctl->epoch_cur = epoch; }
 }
 
 // ------------------------------------------------------------------------------------
@@ -865,6 +878,7 @@ struct PackArgs {
     int *out_newton, *out_nbr;
     const Ctl *ctl;
     int pad, na, ng;
+    unsigned idx_base;   // global index of the first local particle (x-slabs), else 0
 };
 
 __global__ void k_unpack(PackArgs A) {
@@ -887,14 +901,14 @@ __global__ void k_unpack(PackArgs A) {
 
 __global__ void k_pack(PackArgs A) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    const int ng = A.ctl->GL + A.ctl->GR;
+    const int ng = A.ng;
     if (t >= A.na + ng) return;
     int s, out;
     const double *vv, *uu;
     int type;
     if (t < A.na) {
         s = A.pad + t;
-        out = (int)A.idx[s];
+        out = (int)(A.idx[s] - A.idx_base);
         vv = A.v; uu = A.u; type = 0;
     } else {
         s = A.gorder[t - A.na];
@@ -916,17 +930,140 @@ __global__ void k_pack(PackArgs A) {
 
 // one double per particle, sorted slot -> array-index order (same mapping as k_pack)
 __global__ void k_pack_f64(const double *src, double *out, const unsigned *idx, const int *gorder, const Ctl *ctl,
-                           int pad, int na) {
+                           int pad, int na, int ng, unsigned idx_base) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    const int ng = ctl->GL + ctl->GR;
     if (t >= na + ng) return;
     if (t < na) {
         const int s = pad + t;
-        out[idx[s]] = src[s];
+        out[idx[s] - idx_base] = src[s];
     } else {
         out[t] = src[gorder[t - na]];
     }
 }
+
+// ------------------------------------------------------------------------------------
+// x-slab decomposition: the K particles next to a slab edge travel to the
+// neighbouring rank and fill ITS pad on the facing side, in the same ascending-x order, so that
+// every kernel above runs unchanged.  Messages are rows of K doubles plus a header row.
+//   BASE    after the drift:  x, m, v_half, u_half, h_old, rho_old, P, idx            (8 rows)
+//   RECORDS after the density pass: the owner's Rec2                                   (8 rows)
+//   ITERATE during the ordered sweep: current fully kicked v, u                        (2 rows)
+// header[0] = number of particles in the message.
+enum { MSG_BASE = 0, MSG_RECORDS = 1, MSG_ITERATE = 2 };
+__host__ __device__ inline int msg_rows(int what) { return what == MSG_ITERATE ? 2 : 8; }
+
+struct SlabArgs {
+    double *x, *m, *vh, *uh, *vn, *un, *h, *rho, *P;
+    unsigned *idx;
+    Rec2 *rec;
+    int *dirty;
+    int *wl[2];
+    Ctl *ctl;
+    int pad, na, K;
+    int side;        // -1: my left edge / my left pad, +1: right
+};
+
+// my edge particles -> message (side = which of my edges)
+__global__ void k_slab_pack(SlabArgs A, int what, double *buf) {
+    const int cnt = min(A.K, A.na);
+    const int first = A.side < 0 ? A.pad : A.pad + A.na - cnt;
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < cnt; k += gridDim.x * blockDim.x) {
+        const int s = first + k;
+        if (what == MSG_BASE) {
+            buf[0 * A.K + k] = A.x[s]; buf[1 * A.K + k] = A.m[s]; buf[2 * A.K + k] = A.vh[s];
+            buf[3 * A.K + k] = A.uh[s]; buf[4 * A.K + k] = A.h[s]; buf[5 * A.K + k] = A.rho[s];
+            buf[6 * A.K + k] = A.P[s]; buf[7 * A.K + k] = (double)A.idx[s];
+        } else if (what == MSG_RECORDS) {
+            const Rec2 r = A.rec[s];
+            buf[0 * A.K + k] = r.A.h; buf[1 * A.K + k] = r.A.c5; buf[2 * A.K + k] = r.A.rho; buf[3 * A.K + k] = r.A.kap;
+            buf[4 * A.K + k] = r.B.h; buf[5 * A.K + k] = r.B.c5; buf[6 * A.K + k] = r.B.rho; buf[7 * A.K + k] = r.B.kap;
+        } else {
+            buf[0 * A.K + k] = A.vn[s]; buf[1 * A.K + k] = A.un[s];
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        buf[msg_rows(what) * A.K] = (double)cnt;
+        if (what == MSG_ITERATE) A.ctl->halo_changed = 0;   // the unpack that follows this exchange sets it again
+    }
+}
+
+// message from the neighbour on `side` -> my pad on that side.  One CTA.
+__global__ void __launch_bounds__(1024) k_slab_unpack(SlabArgs A, int what, const double *buf) {
+    Ctl *ctl = A.ctl;
+    const int cnt = (int)buf[msg_rows(what) * A.K];
+    if (cnt < 0 || cnt > A.K || cnt > A.pad) {
+        if (threadIdx.x == 0) raise(ctl, E_CAPACITY, -1);
+        return;
+    }
+    // a message from my LEFT neighbour holds ITS last particles: they end right before my first one
+    const int first = A.side < 0 ? A.pad - cnt : A.pad + A.na;
+    __shared__ int s_changed, s_tile;
+    if (threadIdx.x == 0) { s_changed = 0; s_tile = A.side < 0 ? -1 : 0x7fffffff; }
+    __syncthreads();
+    const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
+    const int ntiles = (A.na + kTile - 1) / kTile;
+    for (int k = threadIdx.x; k < cnt; k += blockDim.x) {
+        const int s = first + k;
+        if (what == MSG_BASE) {
+            A.x[s] = buf[0 * A.K + k]; A.m[s] = buf[1 * A.K + k];
+            const double v = buf[2 * A.K + k], u = buf[3 * A.K + k];
+            A.vh[s] = v; A.uh[s] = u;
+            A.vn[s] = v; A.un[s] = u;            // first guess of the neighbour's fully kicked values
+            A.h[s] = buf[4 * A.K + k]; A.rho[s] = buf[5 * A.K + k]; A.P[s] = buf[6 * A.K + k];
+            A.idx[s] = (unsigned)buf[7 * A.K + k];
+        } else if (what == MSG_RECORDS) {
+            Rec2 r;
+            r.A.h = buf[0 * A.K + k]; r.A.c5 = buf[1 * A.K + k]; r.A.rho = buf[2 * A.K + k]; r.A.kap = buf[3 * A.K + k];
+            r.B.h = buf[4 * A.K + k]; r.B.c5 = buf[5 * A.K + k]; r.B.rho = buf[6 * A.K + k]; r.B.kap = buf[7 * A.K + k];
+            A.rec[s] = r;
+            // the scan bound of the force pass must cover the neighbour's smoothing lengths too
+            atomicMax(&ctl->hmax_bits, (unsigned long long)__double_as_longlong(fmax(r.A.h, r.B.h)));
+        } else {
+            const double v = buf[0 * A.K + k], u = buf[1 * A.K + k];
+            if (__double_as_longlong(v) != __double_as_longlong(A.vn[s]) ||
+                __double_as_longlong(u) != __double_as_longlong(A.un[s])) {
+                A.vn[s] = v; A.un[s] = u;
+                s_changed = 1;
+                // own tiles holding a particle within reach of this halo particle
+                const double xj = A.x[s];
+                if (A.side < 0) {
+                    int q = A.pad;
+                    while (q < A.pad + A.na && A.x[q] - xj < kRadius * Hb) q++;
+                    if (q > A.pad) atomicMax(&s_tile, (q - 1 - A.pad) / kTile);
+                } else {
+                    int q = A.pad + A.na - 1;
+                    while (q >= A.pad && xj - A.x[q] < kRadius * Hb) q--;
+                    if (q < A.pad + A.na - 1) atomicMin(&s_tile, (q + 1 - A.pad) / kTile);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (what == MSG_BASE && threadIdx.x == 0) {
+        if (A.side < 0) { ctl->GL = cnt; ctl->halo_left = 1; } else { ctl->GR = cnt; ctl->halo_right = 1; }
+        // the slabs must stay ordered across the edge too: a particle that overtook its neighbour on
+        // the other rank has to migrate (sphb_slab_* callers rebalance when they see this code)
+        if (cnt > 0 && A.na > 0) {
+            const bool bad = A.side < 0 ? (A.x[A.pad - 1] > A.x[A.pad]) : (A.x[A.pad + A.na - 1] > A.x[A.pad + A.na]);
+            if (bad) raise(ctl, E_UNSORTED, A.side < 0 ? A.pad : A.pad + A.na - 1);
+        }
+    }
+    if (what == MSG_ITERATE && s_changed) {
+        // queue those tiles for the next sweep, exactly like a changed particle of my own would
+        const int epoch = ctl->epoch_cur;
+        const int ta = A.side < 0 ? 0 : min(s_tile, ntiles);
+        const int tb = A.side < 0 ? min(s_tile, ntiles - 1) : ntiles - 1;
+        for (int t = ta + threadIdx.x; t <= tb; t += blockDim.x) {
+            if (atomicMax(A.dirty + t, epoch) < epoch) {
+                const int slot = atomicAdd(&ctl->nwork[(epoch + 1) & 1], 1);
+                A.wl[(epoch + 1) & 1][slot] = t;
+            }
+        }
+        if (threadIdx.x == 0) ctl->halo_changed = 1;
+    }
+}
+
+__global__ void k_slab_flags(Ctl *ctl, int hl, int hr) { ctl->halo_left = hl; ctl->halo_right = hr; }
 
 // ------------------------------------------------------------------------------------
 // sort support
@@ -951,21 +1088,22 @@ struct LatticeArgs {
     unsigned *idx;
     int *slot_id;
     int pad, na;
+    long long i0;      // global index of this handle's first particle (x-slabs)
     double min_x, spacing, v0, u0, h0, mass;
 };
 __global__ void k_lattice(LatticeArgs A) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= A.na) return;
     const int s = A.pad + i;
-    const double pos = __dadd_rn(A.min_x, __dmul_rn(A.spacing, (double)i));
+    const double pos = __dadd_rn(A.min_x, __dmul_rn(A.spacing, (double)(A.i0 + i)));
     A.x[s] = pos;
     A.v[s] = (pos < 0) ? A.v0 : -A.v0;
     A.u[s] = A.u0;
     A.h[s] = A.h0;
     A.m[s] = A.mass;
     A.a[s] = 0; A.du[s] = 0; A.rho[s] = 0; A.P[s] = 0;
-    A.idx[s] = (unsigned)i;
-    A.slot_id[i] = i;
+    A.idx[s] = (unsigned)(A.i0 + i);
+    A.slot_id[i] = (int)(A.i0 + i);
 }
 __global__ void k_prepass(const double *x, double *v, const double *u, const double *rho, double *P, int pad,
                           int na) {
@@ -984,6 +1122,7 @@ __global__ void k_begin(Ctl *ctl, int clear_cand) {
     if (clear_cand) ctl->ncand = 0;
     ctl->nwork[0] = 0;
     ctl->nwork[1] = 0;
+    ctl->halo_changed = 0;
     ctl->force_pairs = 0ull;
 }
 
