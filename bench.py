@@ -208,10 +208,14 @@ def run_ours(args, name, n, pc, varh):
 
     kw = workload_kwargs(n, pc, varh)
     cfg = Config(n_part=n, mass=kw["mass"], pressure_calc=pc, t_i=kw["t_i"])
-    stream = torch.cuda.Stream()
-    from sph_b200.slabs import make_simulation   # 1 rank: a plain Simulation; >1: x-slabs with halos
-    sim = make_simulation(cfg, variable_h=varh, fixed_h=kw["constant_h"], device=local, rank=rank, world=world)
-    sim.set_stream(stream.cuda_stream)
+    from sph_b200.slabs import make_simulation   # 1 rank: a plain Simulation; >1: this rank's x-slab
+    sim = make_simulation(cfg, variable_h=varh, fixed_h=kw["constant_h"], device=local, rank=rank, world=world,
+                          halo_count=args.halo)
+    if world > 1:
+        stream = sim.stream                      # handle, halo messages and NCCL calls share it
+    else:
+        stream = torch.cuda.Stream()
+        sim.set_stream(stream.cuda_stream)
     sim.init_lattice()
 
     def barrier():
@@ -260,6 +264,11 @@ def run_ours(args, name, n, pc, varh):
     sim.set_profiling(False)
     c2 = sim.counters()
     n_local = c2.n_alive
+    if world > 1:     # statistics below are per rank; take the busiest phase times over ranks
+        for k in list(phases):
+            t = torch.tensor([phases[k][0]], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            phases[k] = (float(t.item()), phases[k][1])
     hist = c2.newton_hist
     tot = max(sum(hist), 1)
     newton_mean = sum(k * v for k, v in enumerate(hist)) / tot if varh else 0.0
@@ -294,30 +303,39 @@ def run_ours(args, name, n, pc, varh):
 
     # ---- end to end through the C-ABI with HOST buffers, every step: upload + step + download
     e2e = None
-    if world == 1:
+    if True:
+        # every rank moves ITS particles (the whole set on one GPU, its slab otherwise) through host memory
         e2e_steps = max(1, min(args.steps, 3))
-        nbuf = n + 2 * 4096
+        hs = sim if world == 1 else sim.ranks[0]     # the object that owns this rank's handle
+        n_loc = n_local
+        nbuf = n_loc + 2 * 4096
         host = torch.empty(nbuf * PARTICLE_DTYPE.itemsize, dtype=torch.uint8, pin_memory=True)
         rec_arr = host.numpy().view(PARTICLE_DTYPE)
-        out, ng = sim.download(rec_arr)
+        out, ng = hs.download(rec_arr)
         barrier()
         h2d = d2h = 0
-        ev0.record(stream)
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            npart = len(out)
-            sim.upload(rec_arr[:npart], ng)
-            h2d += npart * PARTICLE_DTYPE.itemsize
-            sim.step(1)
-            out, ng = sim.download(rec_arr)
-            d2h += len(out) * PARTICLE_DTYPE.itemsize
-        ev1.record(stream)
+        with torch.cuda.stream(stream):
+            ev0.record(stream)
+            for _ in range(e2e_steps):
+                npart = len(out)
+                hs.upload(rec_arr[:npart], ng)
+                h2d += npart * PARTICLE_DTYPE.itemsize
+                sim.step(1)
+                out, ng = hs.download(rec_arr)
+                d2h += len(out) * PARTICLE_DTYPE.itemsize
+            ev1.record(stream)
         barrier()
         e2e_ms = ev0.elapsed_time(ev1)
+        if world > 1:
+            t = torch.tensor([e2e_ms, float(h2d), float(d2h)], device="cuda", dtype=torch.float64)
+            tmax = t.clone()
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            e2e_ms, h2d, d2h = float(tmax[0].item()), int(t[1].item()), int(t[2].item())
         e2e = {"value": n * e2e_steps / (e2e_ms * 1e-3), "unit": UNIT, "steps": e2e_steps,
                "h2d_bytes_per_step": h2d // e2e_steps, "d2h_bytes_per_step": d2h // e2e_steps,
                "ms_per_step": e2e_ms / e2e_steps,
-               "route": "sphb_upload(pinned Particle[]) + sphb_step(1) + sphb_download(Particle[])"}
+               "route": "sphb_upload(pinned Particle[]) + sphb_step(1) + sphb_download(Particle[]), all ranks"}
     sim.close()
 
     cpu = None
@@ -335,7 +353,8 @@ def run_ours(args, name, n, pc, varh):
             "config": {"workload": name, "n_particles": n, "pressure_calc": "adiabatic" if pc == 1 else "isothermal",
                        "smoothing_length": "variable (Newton/bisection per particle)" if varh else "fixed, 5 spacings",
                        "order": "reference (index-ordered in-place sweep, exact)", "sweeps_per_step": sweeps_mean,
-                       "parallelism": "x-slabs x%d" % world if world > 1 else "single GPU",
+                       "parallelism": ("x-slabs x%d, %d-particle halos over NCCL send/recv, %d exchange rounds in the last step"
+                                       % (world, args.halo, sim.rounds_last)) if world > 1 else "single GPU",
                        "l2": "state arrays (%.1f GB) larger than L2, no flush needed" % (n * 8 * 20 / 1e9)},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
     print(json.dumps(line), flush=True)
@@ -351,6 +370,7 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--n", type=int, default=0, help="override the particle count of the workload")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--halo", type=int, default=256, help="particles exchanged per slab edge (x-slab runs)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3

@@ -890,7 +890,7 @@ __global__ void k_unpack(PackArgs A) {
         const int s = A.pad + i;
         A.x[s] = r.pos; A.v[s] = r.vel; A.u[s] = r.u; A.a[s] = r.acc; A.du[s] = r.du_dt;
         A.h[s] = r.h; A.rho[s] = r.density; A.P[s] = r.pressure; A.m[s] = r.mass;
-        A.idx[s] = (unsigned)i;
+        A.idx[s] = (unsigned)i + A.idx_base;
     } else {
         const int k = i - A.na;
         A.gx[k] = r.pos; A.gv[k] = r.vel; A.gu[k] = r.u; A.ga[k] = r.acc; A.gdu[k] = r.du_dt;

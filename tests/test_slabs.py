@@ -132,3 +132,20 @@ def test_too_thin_a_halo_is_reported():
         many.step(1)
     assert e.value.code == 13
     many.close()
+
+
+@pytest.mark.gpu
+def test_slabs_over_nccl_match_single_handle():
+    """One process per GPU, NCCL send/recv (needs >= 2 GPUs on the box; skipped otherwise)."""
+    import subprocess
+    import torch
+    ngpu = torch.cuda.device_count()
+    if ngpu < 2:
+        pytest.skip("needs at least 2 GPUs")
+    world = min(ngpu, 4)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+           os.path.join(ROOT, "tests", "dist_slab_check.py")]
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    assert res.returncode == 0, res.stdout[-3000:]
+    assert "DIFFERS" not in res.stdout
