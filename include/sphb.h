@@ -169,7 +169,9 @@ int sphb_get_phase_times(sphb_handle *h, double *ms, long long *launches, int re
  * and unpacks messages in caller-owned DEVICE buffers of sphb_slab_message_doubles() doubles; moving
  * them (NCCL send/recv, or a device copy) is the caller's job.  side: -1 = left neighbour, +1 = right.
  * Step: step_begin | exchange BASE | density | exchange RECORDS | force_first, refine |
- *       { exchange ITERATE | refine } until no rank reports halo_changed | step_end.               */
+ *       { exchange ITERATE | refine } a fixed number of rounds | exchange ITERATE | poll (the step's one
+ *       host synchronisation) | ranks agree on MAX(flags): error -> raise; order broken -> resort and
+ *       repeat from 'exchange BASE'; halo changed -> more rounds; else step_end.                    */
 enum { SPHB_MSG_BASE = 0, SPHB_MSG_RECORDS = 1, SPHB_MSG_ITERATE = 2 };
 /* this handle holds global particle indices [index_offset, index_offset + n_alive) of n_global;
  * halo_count particles travel per edge (must exceed the kernel reach in particles; too thin a halo is
@@ -183,7 +185,9 @@ int sphb_slab_step_begin(sphb_handle *h);   /* kick-drift, order check (+ sort),
 int sphb_slab_density(sphb_handle *h);      /* density + root-find + omega + records of own particles */
 int sphb_slab_force_first(sphb_handle *h);  /* first force sweep + second kick */
 int sphb_slab_refine(sphb_handle *h);       /* ordered-sweep refinement until the local work list is empty */
-int sphb_slab_poll(sphb_handle *h, int *halo_changed);   /* did the last ITERATE unpack change anything here? */
+int sphb_slab_poll(sphb_handle *h, int *flags3);  /* {device error code, x-order broken, halo iterate changed} */
+int sphb_slab_resort(sphb_handle *h);       /* after a poll saw 'order broken' on some rank */
+int sphb_slab_raise(sphb_handle *h);        /* the polled error code as status + message */
 int sphb_slab_step_end(sphb_handle *h);
 /* t = 0 in phases: init_lattice | [adiabatic: exchange BASE | sphb_density(h,0) | prepass] | sphb_ghosts |
  * exchange BASE | sphb_density(h,1) | records | exchange RECORDS | forces */

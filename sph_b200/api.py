@@ -145,7 +145,7 @@ def load_library():
     L.sphb_slab_message_doubles.argtypes = [p, i]
     L.sphb_slab_pack.argtypes = [p, i, i, p]
     L.sphb_slab_unpack.argtypes = [p, i, i, p]
-    for name in ('step_begin', 'density', 'force_first', 'refine', 'step_end', 'init_lattice', 'prepass', 'records', 'forces'):
+    for name in ('step_begin', 'density', 'force_first', 'refine', 'step_end', 'init_lattice', 'prepass', 'records', 'forces', 'resort', 'raise'):
         getattr(L, 'sphb_slab_' + name).argtypes = [p]
     L.sphb_slab_poll.argtypes = [p, ip]
     L.sphb_density_static.argtypes = [p, p, p, i, d, d, d, i, p, p, p]

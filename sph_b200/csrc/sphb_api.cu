@@ -32,7 +32,8 @@ struct sphb_handle {
            *rho = nullptr, *P = nullptr, *m = nullptr;
     // per-step work arrays
     double *xalt = nullptr, *vh = nullptr, *uh = nullptr, *vn = nullptr, *un = nullptr, *hn = nullptr,
-           *rhon = nullptr, *omn = nullptr, *oms = nullptr, *Pn = nullptr, *tmp = nullptr;
+           *rhon = nullptr, *omn = nullptr, *oms = nullptr, *Pn = nullptr, *tmp = nullptr, *an = nullptr,
+           *dun = nullptr;   // acc, du_dt of the step in flight (swapped in by step_finish)
     unsigned *idx = nullptr, *idx_alt = nullptr;
     int *slot_id = nullptr, *cnt = nullptr, *dirty = nullptr, *cand = nullptr, *gorder = nullptr,
         *perm = nullptr, *iota = nullptr, *wl0 = nullptr, *wl1 = nullptr;
@@ -58,6 +59,7 @@ struct sphb_handle {
     double m0 = 0.0;
     bool have_counts = false;
     long long steps = 0, sweeps_total = 0, sorts = 0;
+    unsigned long long fallbacks_committed = 0;   // bisection fallbacks of finished steps (a repeated attempt restarts from it)
     int sweeps_last = 0;
     int epoch = 8;
     int refine_grid = 0;
@@ -225,8 +227,10 @@ int sort_alive(sphb_handle *H, bool full) {
 
 // Place ghosts into the pads. from_alive: mirror the selected candidates out of (vs,us);
 // otherwise the staging arrays were filled by the upload.  Ghost v,u go to the pads of (vd,ud).
-int launch_ghost_build(sphb_handle *H, int from_alive, int nstaged, double *vs, double *us, double *vd, double *ud) {
+int launch_ghost_build(sphb_handle *H, int from_alive, int nstaged, double *vs, double *us, double *vd, double *ud,
+                       bool into_next = false) {
     GhostArgs G;
+    G.ad = into_next ? H->an : H->a; G.dud = into_next ? H->dun : H->du;
     G.x = H->x; G.vd = vd; G.ud = ud; G.a = H->a; G.du = H->du; G.h = H->h; G.rho = H->rho; G.P = H->P; G.m = H->m;
     G.vs = vs; G.us = us; G.idx = H->idx; G.cand = H->cand;
     G.gx = H->gx; G.gv = H->gv; G.gu = H->gu; G.ga = H->ga; G.gdu = H->gdu; G.gh = H->gh; G.grho = H->grho;
@@ -306,10 +310,16 @@ SweepArgs sweep_args(sphb_handle *H) {
     return A;
 }
 
-// SPHSimulation::step_forward (sph_simulation.cpp:55-108) in four phases; between them an x-slab
-// run exchanges halos with its neighbours (sphb_slab_*), a single-GPU run just goes on.
-int step_begin(sphb_handle *H) {   // kick-drift, order check (+ sort), wall ghosts
-    if (H->epoch > 0x7fff0000 - 2 * H->opt.max_sweeps) {   // stamp wrap-around
+// SPHSimulation::step_forward (sph_simulation.cpp:55-108) in phases; between them an x-slab run
+// exchanges halos with its neighbours (sphb_slab_*), a single-GPU run just goes on.
+//
+// The x-order check is optimistic: the kick-drift kernel raises a flag when two neighbours swapped
+// places, everything after it runs regardless and writes only into the next-state buffers, and
+// the flag is looked at together with the error word at the ONE host synchronisation at the end
+// of the step.  In the rare step where it is set, the alive block is radix-sorted and the phases
+// after the drift run again; nothing of the previous state has been overwritten by then.
+int step_begin(sphb_handle *H) {   // kick-drift + order flag, wall ghosts
+    if (H->epoch > 0x7fff0000 - 4 * H->opt.max_sweeps) {   // stamp wrap-around
         CK(cudaMemsetAsync(H->dirty, 0, sizeof(int) * (size_t)nblk(H->cap_alive, kTile), H->stream));
         H->epoch = 8;
     }
@@ -317,17 +327,27 @@ int step_begin(sphb_handle *H) {   // kick-drift, order check (+ sort), wall gho
     TRY(launch_begin(H, 1));
     TRY(launch_kick(H, 1));
     phase_end(H, 0);
-    // the order check decides on the host whether the radix sort runs
-    TRY(read_ctl(H));
-    if (H->h_ctl->unsorted || H->opt.sort_every_step) {
+    if (H->opt.sort_every_step) {
         TRY(sort_alive(H, false));
         TRY(launch_begin(H, 1));
         TRY(launch_kick(H, 0));   // ghost candidates refer to sorted slots: select again
         phase_end(H, 1);
     }
-    TRY(launch_ghost_build(H, 1, 0, H->vh, H->uh, H->vh, H->uh));
+    TRY(launch_ghost_build(H, 1, 0, H->vh, H->uh, H->vh, H->uh, true));
     H->ghost_in_half = true;
     phase_end(H, 2);
+    return SPHB_OK;
+}
+
+// after an attempt found the order flag set: sort, re-select the ghost candidates, rebuild the ghosts
+int step_resort(sphb_handle *H) {
+    CK(cudaMemcpyAsync(&H->d_ctl->fallbacks, &H->fallbacks_committed, sizeof(unsigned long long),
+                       cudaMemcpyHostToDevice, H->stream));
+    TRY(sort_alive(H, false));
+    TRY(launch_begin(H, 1));
+    TRY(launch_kick(H, 0));
+    TRY(launch_ghost_build(H, 1, 0, H->vh, H->uh, H->vh, H->uh, true));
+    H->epoch += H->opt.max_sweeps + 2;    // fresh stamps for the second attempt
     return SPHB_OK;
 }
 
@@ -339,6 +359,7 @@ int step_density(sphb_handle *H) {
 
 SweepArgs step_sweep_args(sphb_handle *H) {
     SweepArgs A = sweep_args(H);
+    A.a = H->an; A.du = H->dun;       // the previous a, du stay intact until step_finish
     A.Pstale = H->P; A.Pout = H->Pn;
     A.vh = H->vh; A.uh = H->uh;
     A.F.vA = H->vh; A.F.uA = H->uh;
@@ -363,6 +384,25 @@ int step_refine(sphb_handle *H) {   // runs until this handle's work list is emp
     return SPHB_OK;
 }
 
+// device flags of the attempt in flight: one small D2H copy + stream synchronisation
+int step_flags(sphb_handle *H, int *err, int *unsorted, int *halo_changed) {
+    CK(cudaMemcpyAsync(H->h_ctl, H->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaStreamSynchronize(H->stream));
+    *err = H->h_ctl->err_code;
+    *unsorted = H->h_ctl->unsorted;
+    *halo_changed = H->h_ctl->halo_changed;
+    return SPHB_OK;
+}
+
+int step_error(sphb_handle *H) {    // turn the error word just read into a status
+    char b[256];
+    snprintf(b, sizeof b, "%s (sorted slot %d)", err_text(H->h_ctl->err_code), H->h_ctl->err_particle);
+    H->err = b;
+    const int code = H->h_ctl->err_code;
+    CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, 2 * sizeof(int), H->stream));
+    return code;
+}
+
 int step_finish(sphb_handle *H) {
     H->epoch += H->opt.max_sweeps + 2;
     std::swap(H->v, H->vn);
@@ -370,15 +410,37 @@ int step_finish(sphb_handle *H) {
     std::swap(H->h, H->hn);
     std::swap(H->rho, H->rhon);
     std::swap(H->P, H->Pn);
+    std::swap(H->a, H->an);
+    std::swap(H->du, H->dun);
     H->steps++;
+    H->fallbacks_committed = H->h_ctl->fallbacks;
+    const int used = (H->opt.order == SPHB_ORDER_JACOBI) ? 1 : H->h_ctl->sweeps_used;
+    H->sweeps_last = used;
+    H->sweeps_total += used;
+    H->cfg.n_ghost = wall_ghosts(H);
+    H->cfg.n_part = H->na + H->cfg.n_ghost;
+    phase_collect(H);
     return SPHB_OK;
 }
 
 int step_once(sphb_handle *H) {
     TRY(step_begin(H));
-    TRY(step_density(H));
-    TRY(step_force_first(H));
-    TRY(step_refine(H));
+    for (int attempt = 0;; attempt++) {
+        TRY(step_density(H));
+        TRY(step_force_first(H));
+        TRY(step_refine(H));
+        int err, unsorted, changed;
+        TRY(step_flags(H, &err, &unsorted, &changed));
+        if (unsorted && attempt == 0) {
+            // whatever the kernels complained about came from the broken order: forget it, sort, redo
+            CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, 2 * sizeof(int), H->stream));
+            TRY(step_resort(H));
+            continue;
+        }
+        if (unsorted) { H->err = err_text(SPHB_ERR_UNSORTED); return SPHB_ERR_UNSORTED; }
+        if (err) return step_error(H);
+        break;
+    }
     return step_finish(H);
 }
 
@@ -527,7 +589,7 @@ int sphb_create(const sphb_config *cfg, const sphb_options *opt_in, sphb_handle 
     H->m0 = cfg->mass;
     const size_t T = (size_t)H->total;
     double **darr[] = {&H->x, &H->v, &H->u, &H->a, &H->du, &H->h, &H->rho, &H->P, &H->m, &H->xalt, &H->vh,
-                       &H->uh, &H->vn, &H->un, &H->hn, &H->rhon, &H->omn, &H->oms, &H->Pn, &H->tmp};
+                       &H->uh, &H->vn, &H->un, &H->hn, &H->rhon, &H->omn, &H->oms, &H->Pn, &H->tmp, &H->an, &H->dun};
     for (double **p : darr) { int rc = dalloc(H, p, T); if (rc) return fail(rc); }
     double **garr[] = {&H->gx, &H->gv, &H->gu, &H->ga, &H->gdu, &H->gh, &H->grho, &H->gP, &H->gm};
     for (double **p : garr) { int rc = dalloc(H, p, (size_t)H->cand_cap); if (rc) return fail(rc); }
@@ -558,7 +620,7 @@ void sphb_destroy(sphb_handle *H) {
     if (!H || H == &g_null_handle_for_errors) return;
     cudaSetDevice(H->device);
     if (H->stream) cudaStreamSynchronize(H->stream);
-    void *ptrs[] = {H->x, H->v, H->u, H->a, H->du, H->h, H->rho, H->P, H->m, H->xalt, H->vh, H->uh, H->vn, H->un,
+    void *ptrs[] = {H->an, H->dun, H->x, H->v, H->u, H->a, H->du, H->h, H->rho, H->P, H->m, H->xalt, H->vh, H->uh, H->vn, H->un,
                     H->hn, H->rhon, H->omn, H->oms, H->Pn, H->tmp, H->gx, H->gv, H->gu, H->ga, H->gdu, H->gh,
                     H->grho, H->gP, H->gm, H->idx, H->idx_alt, H->slot_id, H->cnt, H->dirty, H->cand, H->gorder,
                     H->perm, H->iota, H->gkey, H->d_ctl, H->cub_tmp, H->d_aos, H->d_newton, H->d_nbr,
@@ -766,19 +828,9 @@ int sphb_omega(sphb_handle *H, double *omega, int cap) {
 
 int sphb_step(sphb_handle *H, int nsteps) {
     if (!H || nsteps < 0) return SPHB_ERR_INVALID;
+    if (H->slab) { H->err = "x-slab runs step phase by phase (sphb_slab_*), with halo exchanges in between"; return SPHB_ERR_INVALID; }
     CK(cudaSetDevice(H->device));
-    for (int k = 0; k < nsteps; k++) {
-        TRY(step_once(H));
-        // errors and the sweep count of this step surface at the next read of the control
-        // block; read it here so that every step is accounted (one small D2H per step)
-        TRY(read_ctl(H));
-        phase_collect(H);
-        const int used = (H->opt.order == SPHB_ORDER_JACOBI) ? 1 : H->h_ctl->sweeps_used;
-        H->sweeps_last = used;
-        H->sweeps_total += used;
-    }
-    H->cfg.n_ghost = wall_ghosts(H);
-    H->cfg.n_part = H->na + H->cfg.n_ghost;
+    for (int k = 0; k < nsteps; k++) TRY(step_once(H));   // one host synchronisation per step (its flags)
     return SPHB_OK;
 }
 
@@ -908,28 +960,37 @@ int sphb_slab_refine(sphb_handle *H) {
     CK(cudaSetDevice(H->device));
     return step_refine(H);
 }
-// 1 in *halo_changed: an ITERATE message unpacked since the last call differed from the copy held
-// here, i.e. this rank queued tiles again and the sweep is not known to be finished.
-int sphb_slab_poll(sphb_handle *H, int *halo_changed) {
+// The flags of the attempt in flight (the one host synchronisation of a slab step):
+//   flags[0] error code raised on the device (0 = none), flags[1] x-order broken by the drift,
+//   flags[2] the last ITERATE unpack differed from the copy held here (sweep not known finished).
+// Nothing is raised here: the ranks first agree (MAX over ranks) on what to do.
+int sphb_slab_poll(sphb_handle *H, int *flags) {
+    if (!H || !flags) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    return step_flags(H, &flags[0], &flags[1], &flags[2]);
+}
+// some rank's order flag was set: sort (if mine was), forget the attempt's errors, rebuild the ghosts
+int sphb_slab_resort(sphb_handle *H) {
     if (!H) return SPHB_ERR_INVALID;
     CK(cudaSetDevice(H->device));
-    TRY(read_ctl(H));
-    if (halo_changed) *halo_changed = H->h_ctl->halo_changed;
-    CK(cudaMemsetAsync(&H->d_ctl->halo_changed, 0, sizeof(int), H->stream));
+    CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, 2 * sizeof(int), H->stream));
+    if (H->h_ctl->unsorted) return step_resort(H);
+    TRY(launch_begin(H, 1));
+    TRY(launch_kick(H, 0));
+    TRY(launch_ghost_build(H, 1, 0, H->vh, H->uh, H->vh, H->uh, true));
+    H->epoch += H->opt.max_sweeps + 2;
     return SPHB_OK;
+}
+// turn the error word seen by the last poll into this handle's status and message
+int sphb_slab_raise(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    if (H->h_ctl->err_code == 0) return SPHB_OK;
+    return step_error(H);
 }
 int sphb_slab_step_end(sphb_handle *H) {
     if (!H) return SPHB_ERR_INVALID;
-    CK(cudaSetDevice(H->device));
-    TRY(step_finish(H));
-    TRY(read_ctl(H));
-    phase_collect(H);
-    const int used = (H->opt.order == SPHB_ORDER_JACOBI) ? 1 : H->h_ctl->sweeps_used;
-    H->sweeps_last = used;
-    H->sweeps_total += used;
-    H->cfg.n_ghost = wall_ghosts(H);
-    H->cfg.n_part = H->na + H->cfg.n_ghost;
-    return SPHB_OK;
+    return step_finish(H);
 }
 
 int sphb_get_counters(sphb_handle *H, sphb_counters *out) {

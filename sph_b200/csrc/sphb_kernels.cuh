@@ -767,6 +767,7 @@ __global__ void __launch_bounds__(kTile) k_check_sorted(const double *x, Ctl *ct
 // them in alive-index order).  One CTA: the candidate count is O(10) at any N.
 struct GhostArgs {
     double *x, *vd, *ud, *a, *du, *h, *rho, *P, *m;   // vd/ud: the v,u arrays the ghosts live in
+    double *ad, *dud;                                  // the acc, du_dt arrays the ghosts live in (a, du: sources)
     const double *vs, *us;                             // the v,u arrays the sources are read from
     unsigned *idx;
     const int *cand;
@@ -833,8 +834,8 @@ __global__ void __launch_bounds__(1024) k_ghost_build(GhostArgs G) {
         G.x[dest] = xc;
         G.vd[dest] = G.gv[c];
         G.ud[dest] = G.gu[c];
-        G.a[dest] = G.ga[c];
-        G.du[dest] = G.gdu[c];
+        G.ad[dest] = G.ga[c];
+        G.dud[dest] = G.gdu[c];
         G.h[dest] = G.gh[c];
         G.rho[dest] = G.grho[c];
         G.P[dest] = G.gP[c];
@@ -1023,18 +1024,22 @@ __global__ void __launch_bounds__(1024) k_slab_unpack(SlabArgs A, int what, cons
             if (__double_as_longlong(v) != __double_as_longlong(A.vn[s]) ||
                 __double_as_longlong(u) != __double_as_longlong(A.un[s])) {
                 A.vn[s] = v; A.un[s] = u;
-                s_changed = 1;
-                // own tiles holding a particle within reach of this halo particle
+                // Only particles that see this neighbour in its NEW state depend on the value: own
+                // particles within reach whose array index is higher (the sweep reaches them later).
+                // Without one, the new value is merely kept.
                 const double xj = A.x[s];
+                const unsigned idxj = A.idx[s];
+                bool relevant = false;
                 if (A.side < 0) {
                     int q = A.pad;
-                    while (q < A.pad + A.na && A.x[q] - xj < kRadius * Hb) q++;
-                    if (q > A.pad) atomicMax(&s_tile, (q - 1 - A.pad) / kTile);
+                    while (q < A.pad + A.na && A.x[q] - xj < kRadius * Hb) { relevant |= A.idx[q] > idxj; q++; }
+                    if (relevant) atomicMax(&s_tile, (q - 1 - A.pad) / kTile);
                 } else {
                     int q = A.pad + A.na - 1;
-                    while (q >= A.pad && xj - A.x[q] < kRadius * Hb) q--;
-                    if (q < A.pad + A.na - 1) atomicMin(&s_tile, (q + 1 - A.pad) / kTile);
+                    while (q >= A.pad && xj - A.x[q] < kRadius * Hb) { relevant |= A.idx[q] > idxj; q--; }
+                    if (relevant) atomicMin(&s_tile, (q + 1 - A.pad) / kTile);
                 }
+                if (relevant) s_changed = 1;
             }
         }
     }

@@ -13,9 +13,12 @@ Per step (libsphb does the device work of each phase, see include/sphb.h `sphb_s
     density                    fused density / root-find / omega of the own particles
     exchange RECORDS           owner-computed (h, rho, omega) records of the edge particles
     force_first, refine        first sweep + local convergence of the ordered sweep
-    repeat: exchange ITERATE   current fully kicked (v, u) of the edge particles; a rank whose copy
-            refine             differed re-queues the tiles in reach and converges again
-    until no rank saw a change (one MAX all-reduce of a flag per round)
+    exchange ITERATE, refine   current fully kicked (v, u) of the edge particles; a rank whose copy
+                               differed re-queues the tiles in reach and converges again
+    exchange ITERATE           check: did anything still move?
+    poll + agree               the step's ONE host synchronisation: MAX over ranks of (device error,
+                               x-order broken by the drift, halo still changing) -> raise / sort and
+                               repeat the attempt / more rounds / done
     step_end
 
 There is no data-path collective: every message goes to a direct neighbour (NCCL send/recv through
@@ -94,10 +97,10 @@ class SlabRank(Simulation):
     def call(self, name, *args):
         self._check(getattr(self.L, "sphb_slab_" + name)(self.h, *args))
 
-    def poll(self) -> bool:
-        flag = C.c_int()
-        self._check(self.L.sphb_slab_poll(self.h, C.byref(flag)))
-        return bool(flag.value)
+    def poll(self):
+        flags = (C.c_int * 3)()
+        self._check(self.L.sphb_slab_poll(self.h, flags))
+        return [flags[0], flags[1], flags[2]]
 
 
 class LocalTransport:
@@ -112,8 +115,8 @@ class LocalTransport:
                 # what I send to my right neighbour arrives as its message from the LEFT
                 self.ranks[r.rank + side].recv[(what, -side)].copy_(r.send[(what, side)])
 
-    def any_changed(self, flags: List[bool]) -> bool:
-        return any(flags)
+    def agree(self, flags):
+        return list(flags)
 
 
 def neighbour_exchange(dist, rank: int, world: int, send: dict, recv: dict):
@@ -131,11 +134,12 @@ def neighbour_exchange(dist, rank: int, world: int, send: dict, recv: dict):
             w.wait()
 
 
-def agree_any(dist, flag_tensor, value: bool) -> bool:
-    """True on every rank iff `value` is true on at least one (MAX all-reduce of one int)."""
-    flag_tensor.fill_(1 if value else 0)
+def agree_max(dist, flag_tensor, values):
+    """Element-wise MAX over all ranks of a few small non-negative ints (one all-reduce)."""
+    for k, v in enumerate(values):
+        flag_tensor[k] = int(v)
     dist.all_reduce(flag_tensor, op=dist.ReduceOp.MAX)
-    return bool(flag_tensor.item())
+    return [int(v) for v in flag_tensor.tolist()]
 
 
 class DistTransport:
@@ -145,24 +149,28 @@ class DistTransport:
         import torch
         import torch.distributed as dist
         self.r, self.dist = rank_obj, dist
-        self.flag = torch.zeros(1, dtype=torch.int32, device=rank_obj.device)
+        self.flag = torch.zeros(3, dtype=torch.int32, device=rank_obj.device)
+        self.host_flag = torch.zeros(3, dtype=torch.int32).pin_memory()
 
     def exchange(self, what):
         r = self.r
         neighbour_exchange(self.dist, r.rank, r.world, {s: r.send[(what, s)] for s in r.sides()},
                            {s: r.recv[(what, s)] for s in r.sides()})
 
-    def any_changed(self, flags: List[bool]) -> bool:
-        return agree_any(self.dist, self.flag, any(flags))
+    def agree(self, flags):
+        self.host_flag[:] = self.host_flag.new_tensor([int(v) for v in flags])
+        self.flag.copy_(self.host_flag, non_blocking=True)
+        self.dist.all_reduce(self.flag, op=self.dist.ReduceOp.MAX)
+        return [int(v) for v in self.flag.tolist()]
 
 
 class SlabSimulation:
     """The protocol above over a set of ranks held by THIS process (one with DistTransport, all of them
     with LocalTransport).  Mirrors the Simulation calls the bench and the tests use."""
 
-    def __init__(self, ranks: List[SlabRank], transport, max_rounds: int = 32):
+    def __init__(self, ranks: List[SlabRank], transport, max_rounds: int = 32, fixed_rounds: int = 1):
         import torch
-        self.ranks, self.t, self.max_rounds = ranks, transport, max_rounds
+        self.ranks, self.t, self.max_rounds, self.fixed_rounds = ranks, transport, max_rounds, fixed_rounds
         self.rounds_last = 0
         # every handle, the message copies and the NCCL calls are ordered on ONE stream
         self.stream = torch.cuda.Stream(device=ranks[0].device)
@@ -211,25 +219,55 @@ class SlabSimulation:
         self._exchange(MSG_RECORDS)
         self._all("forces")
 
+    def _attempt(self):
+        """Everything of a step after the drift, up to the flags."""
+        self._exchange(MSG_BASE)
+        self._all("density")
+        self._exchange(MSG_RECORDS)
+        self._all("force_first")
+        self._all("refine")
+        # The first ITERATE exchange replaces the neighbours' GUESS by converged values, so it practically
+        # always changes something: refine without asking.  The last exchange of the fixed schedule only
+        # CHECKS (its unpack raises the halo_changed flag if anything still moved).
+        for _ in range(self.fixed_rounds):
+            self._exchange(MSG_ITERATE)
+            self._all("refine")
+        self._exchange(MSG_ITERATE)
+        return self.fixed_rounds + 1
+
+    def _flags(self):
+        """MAX over all ranks of (device error, order broken, halo changed): the step's host sync."""
+        fl = [0, 0, 0]
+        for r in self.ranks:
+            f = r.poll()
+            fl = [max(a, b) for a, b in zip(fl, f)]
+        mine = fl[0]
+        return self.t.agree(fl), mine
+
     def _step(self, nsteps=1):
         for _ in range(nsteps):
             self._all("step_begin")
-            self._exchange(MSG_BASE)
-            self._all("density")
-            self._exchange(MSG_RECORDS)
-            self._all("force_first")
-            self._all("refine")
-            rounds = 0
-            while True:
-                self._exchange(MSG_ITERATE)
-                rounds += 1
-                # the first exchange replaces the neighbours' GUESS by converged values: it practically
-                # always changes something, so refine without asking; from then on ask
-                if rounds > 1 and not self.t.any_changed([r.poll() for r in self.ranks]):
-                    break
+            rounds = self._attempt()
+            (err, unsorted, changed), mine = self._flags()
+            if unsorted:
+                # some rank's drift swapped two neighbours: those ranks sort, everybody repeats the
+                # attempt (nothing of the previous state has been overwritten)
+                self._all("resort")
+                rounds = self._attempt()
+                (err, unsorted, changed), mine = self._flags()
+                if unsorted:
+                    raise SphbError(11, "x-order still broken after the sort (a particle crossed a slab edge: rebalance)")
+            while changed and not err:
                 if rounds > self.max_rounds:
                     raise SphbError(10, "x-slab ordered sweep did not settle in %d rounds" % self.max_rounds)
                 self._all("refine")
+                self._exchange(MSG_ITERATE)
+                rounds += 1
+                (err, unsorted, changed), mine = self._flags()
+            if err:
+                for r in self.ranks:
+                    r.call("raise")          # raises SphbError with the device's message on the rank that has it
+                raise SphbError(err, "a neighbouring slab reported device error %d" % err)
             self.rounds_last = rounds
             self._all("step_end")
 

@@ -48,7 +48,7 @@ def _routing_worker(rank, world, port, q):
     import torch
     import torch.distributed as dist
     sys.path.insert(0, ROOT)
-    from sph_b200.slabs import LEFT, RIGHT, agree_any, neighbour_exchange
+    from sph_b200.slabs import LEFT, RIGHT, agree_max, neighbour_exchange
     dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
     try:
         send = {LEFT: torch.full((5,), 10.0 * rank - 1), RIGHT: torch.full((5,), 10.0 * rank + 1)}
@@ -63,9 +63,10 @@ def _routing_worker(rank, world, port, q):
             ok &= bool((recv[RIGHT] == 10.0 * (rank + 1) - 1).all())
         else:
             ok &= bool((recv[RIGHT] == 0).all())
-        flag = torch.zeros(1, dtype=torch.int32)
-        ok &= agree_any(dist, flag, rank == world - 1) is True      # one rank saw a change: all go on
-        ok &= agree_any(dist, flag, False) is False
+        flag = torch.zeros(3, dtype=torch.int32)
+        # one rank saw a change, another an error code: everybody learns both
+        ok &= agree_max(dist, flag, [13 if rank == 0 else 0, 0, 1 if rank == world - 1 else 0]) == [13, 0, 1]
+        ok &= agree_max(dist, flag, [0, 0, 0]) == [0, 0, 0]
         q.put((rank, ok))
     finally:
         dist.destroy_process_group()
