@@ -210,7 +210,7 @@ def run_ours(args, name, n, pc, varh):
     cfg = Config(n_part=n, mass=kw["mass"], pressure_calc=pc, t_i=kw["t_i"])
     from sph_b200.slabs import make_simulation   # 1 rank: a plain Simulation; >1: this rank's x-slab
     sim = make_simulation(cfg, variable_h=varh, fixed_h=kw["constant_h"], device=local, rank=rank, world=world,
-                          halo_count=args.halo)
+                          halo_count=args.halo, native=not args.torch_exchange)
     if world > 1:
         stream = sim.stream                      # handle, halo messages and NCCL calls share it
     else:
@@ -336,6 +336,7 @@ def run_ours(args, name, n, pc, varh):
                "h2d_bytes_per_step": h2d // e2e_steps, "d2h_bytes_per_step": d2h // e2e_steps,
                "ms_per_step": e2e_ms / e2e_steps,
                "route": "sphb_upload(pinned Particle[]) + sphb_step(1) + sphb_download(Particle[]), all ranks"}
+    rounds_last = getattr(sim, 'rounds_last', 0)
     sim.close()
 
     cpu = None
@@ -353,8 +354,8 @@ def run_ours(args, name, n, pc, varh):
             "config": {"workload": name, "n_particles": n, "pressure_calc": "adiabatic" if pc == 1 else "isothermal",
                        "smoothing_length": "variable (Newton/bisection per particle)" if varh else "fixed, 5 spacings",
                        "order": "reference (index-ordered in-place sweep, exact)", "sweeps_per_step": sweeps_mean,
-                       "parallelism": ("x-slabs x%d, %d-particle halos over NCCL send/recv, %d exchange rounds in the last step"
-                                       % (world, args.halo, sim.rounds_last)) if world > 1 else "single GPU",
+                       "parallelism": ("x-slabs x%d, %d-particle halos over ncclSend/ncclRecv, %d ITERATE exchanges in the last step"
+                                       % (world, args.halo, rounds_last)) if world > 1 else "single GPU",
                        "l2": "state arrays (%.1f GB) larger than L2, no flush needed" % (n * 8 * 20 / 1e9)},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
     print(json.dumps(line), flush=True)
@@ -370,6 +371,8 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--n", type=int, default=0, help="override the particle count of the workload")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--torch-exchange", action="store_true",
+                    help="x-slab runs: drive the halo exchange from Python (torch.distributed) instead of inside libsphb")
     ap.add_argument("--halo", type=int, default=256, help="particles exchanged per slab edge (x-slab runs)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

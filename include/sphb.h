@@ -196,6 +196,17 @@ int sphb_slab_prepass(sphb_handle *h);
 int sphb_slab_records(sphb_handle *h);
 int sphb_slab_forces(sphb_handle *h);
 
+/* The same protocol driven inside the library: halo messages go to the direct neighbours with
+ * grouped ncclSend/ncclRecv on the handle's stream (libnccl is opened at run time).  Rank 0 makes
+ * an id with sphb_nccl_unique_id, the host program distributes its 128 bytes (MPI_Bcast,
+ * torch.distributed, a file ...), every rank calls sphb_slab_configure and sphb_slab_comm_init, then
+ * all ranks make the same sphb_slab_init_particles / sphb_slab_step calls. */
+int sphb_nccl_unique_id(void *out128);
+int sphb_slab_comm_init(sphb_handle *h, const void *unique_id128);
+int sphb_slab_init_particles(sphb_handle *h);   /* init_particles, setup.cpp:143-228, across the slabs */
+int sphb_slab_step(sphb_handle *h, int nsteps); /* step_forward, sph_simulation.cpp:55-108, across the slabs */
+int sphb_slab_rounds_last(const sphb_handle *h);/* ITERATE exchanges the last step needed */
+
 /* No counterpart in the reference.  The same density / root-find / omega pass as sphb_density,
  * for callers that cannot allocate device memory when they need it (the whole device already
  * belongs to their own arena allocator, or they are inside a section where cudaMalloc's

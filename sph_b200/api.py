@@ -148,6 +148,11 @@ def load_library():
     for name in ('step_begin', 'density', 'force_first', 'refine', 'step_end', 'init_lattice', 'prepass', 'records', 'forces', 'resort', 'raise'):
         getattr(L, 'sphb_slab_' + name).argtypes = [p]
     L.sphb_slab_poll.argtypes = [p, ip]
+    L.sphb_nccl_unique_id.argtypes = [p]
+    L.sphb_slab_comm_init.argtypes = [p, p]
+    L.sphb_slab_init_particles.argtypes = [p]
+    L.sphb_slab_step.argtypes = [p, i]
+    L.sphb_slab_rounds_last.argtypes = [p]
     L.sphb_density_static.argtypes = [p, p, p, i, d, d, d, i, p, p, p]
     L.sphb_build_arch.argtypes = []
     L.sphb_build_arch.restype = C.c_char_p

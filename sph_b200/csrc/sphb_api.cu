@@ -2,6 +2,8 @@
 // in sphb_kernels.cuh.  No CPU fallback exists: without a usable CUDA device every entry
 // point fails with SPHB_ERR_NO_DEVICE / SPHB_ERR_CUDA.
 #include <cub/device/device_radix_sort.cuh>
+#include <dlfcn.h>
+#include <nccl.h>   // types only: the library is opened at run time (sphb_slab_comm_init)
 
 #include <algorithm>
 #include <cmath>
@@ -36,7 +38,8 @@ struct sphb_handle {
            *dun = nullptr;   // acc, du_dt of the step in flight (swapped in by step_finish)
     unsigned *idx = nullptr, *idx_alt = nullptr;
     int *slot_id = nullptr, *cnt = nullptr, *dirty = nullptr, *cand = nullptr, *gorder = nullptr,
-        *perm = nullptr, *iota = nullptr, *wl0 = nullptr, *wl1 = nullptr;
+        *perm = nullptr, *iota = nullptr, *wl0 = nullptr, *wl1 = nullptr, *wl2 = nullptr;
+    int refine_peak = 0;      // largest refinement work list of the previous step
     Rec2 *rec = nullptr;      // force-pass records written by the density pass
     double *gsum = nullptr;   // own-h gradient sums written by the density pass
     // ghost staging (2*pad each)
@@ -55,6 +58,11 @@ struct sphb_handle {
     bool slab = false, halo_l = false, halo_r = false;
     int rank = 0, world = 1, K = 0;
     long long idx_base = 0, n_global = 0;
+    // native exchange (sphb_slab_comm_init): NCCL communicator, message buffers [what][side], agreed flags
+    ncclComm_t comm = nullptr;
+    double *msg_send[3][2] = {}, *msg_recv[3][2] = {};
+    int *d_flags = nullptr, *h_flags = nullptr;
+    int fixed_rounds = 1, rounds_last = 0;
     bool uniform_mass = true;
     double m0 = 0.0;
     bool have_counts = false;
@@ -290,7 +298,10 @@ int launch_refine(sphb_handle *H, SweepArgs A) {
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kTile, 0));
     if (occ < 1) { H->err = "refinement kernel cannot be made resident"; return SPHB_ERR_CUDA; }
     const int ntiles = nblk(H->na, kTile);
-    int grid = std::min(ntiles, occ * H->num_sms);
+    // a grid-wide barrier costs more the more CTAs take part: the few tiles around a front get one CTA
+    // per SM; a step whose predecessor queued many tiles gets every CTA that can be resident
+    const int want = H->refine_peak > 2 * H->num_sms ? occ * H->num_sms : H->num_sms;
+    int grid = std::min(ntiles, want);
     if (grid < 1) grid = 1;
     int max_sweeps = H->opt.max_sweeps;
     void *args[] = {(void *)&A, (void *)&max_sweeps};
@@ -303,7 +314,7 @@ SweepArgs sweep_args(sphb_handle *H) {
     SweepArgs A;
     A.F.x = H->x; A.F.idx = H->idx; A.F.m = H->m;
     A.F.rec = H->rec; A.F.gsum = H->gsum;
-    A.a = H->a; A.du = H->du; A.dirty = H->dirty; A.wl[0] = H->wl0; A.wl[1] = H->wl1; A.ctl = H->d_ctl;
+    A.a = H->a; A.du = H->du; A.dirty = H->dirty; A.wl[0] = H->wl0; A.wl[1] = H->wl1; A.wl[2] = H->wl2; A.ctl = H->d_ctl;
     A.pad = H->pad; A.na = H->na; A.m0 = H->m0; A.half_dt = H->cfg.t_i / 2;
     A.epoch = H->epoch; A.kick = 1;
     A.vn = H->vn; A.un = H->un;
@@ -414,6 +425,7 @@ int step_finish(sphb_handle *H) {
     std::swap(H->du, H->dun);
     H->steps++;
     H->fallbacks_committed = H->h_ctl->fallbacks;
+    H->refine_peak = H->h_ctl->nwork_peak;
     const int used = (H->opt.order == SPHB_ORDER_JACOBI) ? 1 : H->h_ctl->sweeps_used;
     H->sweeps_last = used;
     H->sweeps_total += used;
@@ -510,7 +522,7 @@ SlabArgs slab_args(sphb_handle *H, int side) {
     SlabArgs A;
     A.x = H->x; A.m = H->m; A.vh = H->vh; A.uh = H->uh; A.vn = H->vn; A.un = H->un;
     A.h = H->h; A.rho = H->rho; A.P = H->P; A.idx = H->idx; A.rec = H->rec;
-    A.dirty = H->dirty; A.wl[0] = H->wl0; A.wl[1] = H->wl1; A.ctl = H->d_ctl;
+    A.dirty = H->dirty; A.wl[0] = H->wl0; A.wl[1] = H->wl1; A.wl[2] = H->wl2; A.ctl = H->d_ctl;
     A.pad = H->pad; A.na = H->na; A.K = H->K; A.side = side;
     return A;
 }
@@ -518,6 +530,100 @@ int slab_flags(sphb_handle *H) {
     k_slab_flags<<<1, 1, 0, H->stream>>>(H->d_ctl, H->halo_l ? 1 : 0, H->halo_r ? 1 : 0);
     H->launches++;
     CK(cudaGetLastError());
+    return SPHB_OK;
+}
+}  // namespace
+
+namespace {
+struct NcclApi {
+    void *lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    std::string err;
+    bool load() {
+        if (lib) return true;
+        for (const char *name : {"libnccl.so.2", "libnccl.so"}) {
+            lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+            if (lib) break;
+        }
+        if (!lib) { err = std::string("cannot open libnccl: ") + dlerror(); return false; }
+#define SPHB_SYM(F) F = reinterpret_cast<decltype(F)>(dlsym(lib, "nccl" #F)); if (!F) { err = "libnccl lacks nccl" #F; lib = nullptr; return false; }
+        SPHB_SYM(GetUniqueId) SPHB_SYM(CommInitRank) SPHB_SYM(CommDestroy) SPHB_SYM(Send) SPHB_SYM(Recv)
+        SPHB_SYM(AllReduce) SPHB_SYM(GroupStart) SPHB_SYM(GroupEnd) SPHB_SYM(GetErrorString)
+#undef SPHB_SYM
+        return true;
+    }
+};
+NcclApi g_nccl;
+
+#define NK(call)                                                                          \
+    do {                                                                                  \
+        ncclResult_t r_ = (call);                                                         \
+        if (r_ != ncclSuccess) {                                                          \
+            H->err = std::string(#call) + ": " + g_nccl.GetErrorString(r_);               \
+            return SPHB_ERR_CUDA;                                                         \
+        }                                                                                 \
+    } while (0)
+
+__global__ void k_flags(const Ctl *ctl, int *flags) {
+    flags[0] = ctl->err_code;
+    flags[1] = ctl->unsorted;
+    flags[2] = ctl->halo_changed;
+}
+
+// pack both edges, one grouped send/recv with the neighbours, unpack both pads
+int native_exchange(sphb_handle *H, int what) {
+    const int n = sphb_slab_message_doubles(H, what);
+    for (int k = 0; k < 2; k++) {
+        const int side = k ? 1 : -1;
+        if (k ? H->halo_r : H->halo_l) TRY(sphb_slab_pack(H, what, side, H->msg_send[what][k]));
+    }
+    NK(g_nccl.GroupStart());
+    for (int k = 0; k < 2; k++) {
+        if (!(k ? H->halo_r : H->halo_l)) continue;
+        const int peer = H->rank + (k ? 1 : -1);
+        NK(g_nccl.Send(H->msg_send[what][k], (size_t)n, ncclFloat64, peer, H->comm, H->stream));
+        NK(g_nccl.Recv(H->msg_recv[what][k], (size_t)n, ncclFloat64, peer, H->comm, H->stream));
+    }
+    NK(g_nccl.GroupEnd());
+    for (int k = 0; k < 2; k++) {
+        const int side = k ? 1 : -1;
+        if (k ? H->halo_r : H->halo_l) TRY(sphb_slab_unpack(H, what, side, H->msg_recv[what][k]));
+    }
+    return SPHB_OK;
+}
+
+// everything of a step after the drift, up to the agreed flags (the step's one host synchronisation)
+int native_attempt(sphb_handle *H, int *rounds) {
+    TRY(native_exchange(H, MSG_BASE));
+    TRY(step_density(H));
+    TRY(native_exchange(H, MSG_RECORDS));
+    TRY(step_force_first(H));
+    TRY(step_refine(H));
+    for (int r = 0; r < H->fixed_rounds; r++) {
+        TRY(native_exchange(H, MSG_ITERATE));
+        TRY(step_refine(H));
+    }
+    TRY(native_exchange(H, MSG_ITERATE));     // check only: its unpack raises halo_changed if anything still moved
+    *rounds = H->fixed_rounds + 1;
+    return SPHB_OK;
+}
+
+int native_flags(sphb_handle *H) {   // -> H->h_flags[0..2] = MAX over ranks; H->h_ctl = my control block
+    k_flags<<<1, 1, 0, H->stream>>>(H->d_ctl, H->d_flags);
+    H->launches++;
+    CK(cudaGetLastError());
+    NK(g_nccl.AllReduce(H->d_flags, H->d_flags, 3, ncclInt32, ncclMax, H->comm, H->stream));
+    CK(cudaMemcpyAsync(H->h_flags, H->d_flags, 3 * sizeof(int), cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaMemcpyAsync(H->h_ctl, H->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaStreamSynchronize(H->stream));
     return SPHB_OK;
 }
 }  // namespace
@@ -600,6 +706,7 @@ int sphb_create(const sphb_config *cfg, const sphb_options *opt_in, sphb_handle 
     rc |= dalloc(H, &H->perm, (size_t)H->cap_alive); rc |= dalloc(H, &H->iota, (size_t)H->cap_alive);
     rc |= dalloc(H, &H->gkey, (size_t)H->cand_cap); rc |= dalloc(H, &H->d_ctl, 1);
     rc |= dalloc(H, &H->wl0, (size_t)nblk(H->cap_alive, kTile) + 1); rc |= dalloc(H, &H->wl1, (size_t)nblk(H->cap_alive, kTile) + 1);
+    rc |= dalloc(H, &H->wl2, (size_t)nblk(H->cap_alive, kTile) + 1);
     rc |= dalloc(H, &H->rec, T); rc |= dalloc(H, &H->gsum, T);
     if (rc) return fail(SPHB_ERR_CUDA);
     CKC(cudaMallocHost((void **)&H->h_ctl, sizeof(Ctl)));
@@ -624,8 +731,12 @@ void sphb_destroy(sphb_handle *H) {
                     H->hn, H->rhon, H->omn, H->oms, H->Pn, H->tmp, H->gx, H->gv, H->gu, H->ga, H->gdu, H->gh,
                     H->grho, H->gP, H->gm, H->idx, H->idx_alt, H->slot_id, H->cnt, H->dirty, H->cand, H->gorder,
                     H->perm, H->iota, H->gkey, H->d_ctl, H->cub_tmp, H->d_aos, H->d_newton, H->d_nbr,
-                    H->wl0, H->wl1, H->rec, H->gsum};
+                    H->wl0, H->wl1, H->wl2, H->rec, H->gsum};
     for (void *p : ptrs) if (p) cudaFree(p);
+    if (H->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(H->comm);
+    for (int w = 0; w < 3; w++) for (int k = 0; k < 2; k++) { if (H->msg_send[w][k]) cudaFree(H->msg_send[w][k]); if (H->msg_recv[w][k]) cudaFree(H->msg_recv[w][k]); }
+    if (H->d_flags) cudaFree(H->d_flags);
+    if (H->h_flags) cudaFreeHost(H->h_flags);
     if (H->h_ctl) cudaFreeHost(H->h_ctl);
     for (int i = 0; i <= SPHB_PHASES; i++) if (H->ev[i]) cudaEventDestroy(H->ev[i]);
     if (H->own_stream) cudaStreamDestroy(H->own_stream);
@@ -992,6 +1103,97 @@ int sphb_slab_step_end(sphb_handle *H) {
     if (!H) return SPHB_ERR_INVALID;
     return step_finish(H);
 }
+
+// ------------------------------------------------------------------------------------
+// The same protocol driven from C++: one NCCL communicator per handle, halo messages sent
+// to the direct neighbours with grouped ncclSend/ncclRecv on the handle's stream, the three
+// step flags agreed with one small ncclAllReduce(MAX).  A step costs the host a dozen launches
+// and ONE stream synchronisation.  libnccl is opened at run time (dlopen), so libsphb.so itself
+// has no link-time dependency on it.
+
+int sphb_nccl_unique_id(void *out128) {
+    sphb_handle *H = &g_null_handle_for_errors;
+    if (!out128) return SPHB_ERR_INVALID;
+    if (!g_nccl.load()) { H->err = g_nccl.err; return SPHB_ERR_NO_DEVICE; }
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId");
+    NK(g_nccl.GetUniqueId(reinterpret_cast<ncclUniqueId *>(out128)));
+    return SPHB_OK;
+}
+
+int sphb_slab_comm_init(sphb_handle *H, const void *unique_id128) {
+    if (!H || !unique_id128) return SPHB_ERR_INVALID;
+    if (!H->slab) { H->err = "sphb_slab_configure with world > 1 comes first"; return SPHB_ERR_INVALID; }
+    if (!g_nccl.load()) { H->err = g_nccl.err; return SPHB_ERR_NO_DEVICE; }
+    CK(cudaSetDevice(H->device));
+    ncclUniqueId id;
+    memcpy(&id, unique_id128, sizeof id);
+    NK(g_nccl.CommInitRank(&H->comm, H->world, id, H->rank));
+    for (int what = 0; what < 3; what++)
+        for (int k = 0; k < 2; k++) {
+            const size_t n = (size_t)sphb_slab_message_doubles(H, what);
+            TRY(dalloc(H, &H->msg_send[what][k], n));
+            TRY(dalloc(H, &H->msg_recv[what][k], n));
+        }
+    TRY(dalloc(H, &H->d_flags, 4));
+    CK(cudaMallocHost((void **)&H->h_flags, 4 * sizeof(int)));
+    CK(cudaStreamSynchronize(H->stream));
+    return SPHB_OK;
+}
+
+// init_particles (setup.cpp:143-228) across the slabs, halo exchanges included
+int sphb_slab_init_particles(sphb_handle *H) {
+    if (!H || !H->comm) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    TRY(sphb_slab_init_lattice(H));
+    if (H->cfg.pressure_calc == SPHB_ADIABATIC) {
+        TRY(native_exchange(H, MSG_BASE));
+        TRY(sphb_density(H, 0));
+        TRY(sphb_slab_prepass(H));
+    }
+    TRY(sphb_ghosts(H, nullptr));
+    TRY(native_exchange(H, MSG_BASE));
+    TRY(sphb_density(H, 1));
+    TRY(sphb_slab_records(H));
+    TRY(native_exchange(H, MSG_RECORDS));
+    return sphb_slab_forces(H);
+}
+
+// SPHSimulation::step_forward (sph_simulation.cpp:55-108) on this rank's slab, nsteps times; every
+// rank of the communicator must make the same call
+int sphb_slab_step(sphb_handle *H, int nsteps) {
+    if (!H || nsteps < 0 || !H->comm) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    for (int k = 0; k < nsteps; k++) {
+        TRY(step_begin(H));
+        int rounds = 0;
+        TRY(native_attempt(H, &rounds));
+        TRY(native_flags(H));
+        if (H->h_flags[1]) {
+            // some rank's drift swapped two neighbours: those ranks sort, everybody repeats the attempt
+            TRY(sphb_slab_resort(H));
+            TRY(native_attempt(H, &rounds));
+            TRY(native_flags(H));
+            if (H->h_flags[1]) { H->err = "x-order still broken after the sort (a particle crossed a slab edge)"; return SPHB_ERR_UNSORTED; }
+        }
+        while (H->h_flags[2] && !H->h_flags[0]) {
+            if (rounds > H->opt.max_sweeps) { H->err = "x-slab ordered sweep did not settle"; return SPHB_ERR_NOT_CONVERGED; }
+            TRY(step_refine(H));
+            TRY(native_exchange(H, MSG_ITERATE));
+            rounds++;
+            TRY(native_flags(H));
+        }
+        if (H->h_flags[0]) {
+            if (H->h_ctl->err_code) return step_error(H);
+            H->err = "a neighbouring slab reported a device error";
+            return H->h_flags[0];
+        }
+        H->rounds_last = rounds;
+        TRY(step_finish(H));
+    }
+    return SPHB_OK;
+}
+
+int sphb_slab_rounds_last(const sphb_handle *H) { return H ? H->rounds_last : -1; }
 
 int sphb_get_counters(sphb_handle *H, sphb_counters *out) {
     if (!H || !out) return SPHB_ERR_INVALID;

@@ -50,7 +50,8 @@ struct Ctl {
     int err_code, err_particle;    // first error wins
     unsigned long long hmax_bits;  // max over every h (old and new) in [lo,hi), as ordered bits
     unsigned long long fallbacks;  // bisection fallbacks taken
-    int nwork[2];                  // tiles in the work list of the sweep with even / odd stamp
+    int nwork[3];                  // tiles in the work list of the sweep whose stamp is k mod 3
+    int nwork_peak;                // largest work list of the current step (sizes the next step's refinement grid)
     int sweeps_used;               // force sweeps the last step needed
     int epoch_cur;                 // stamp of the most recent force sweep (handed from launch to launch)
     int halo_left, halo_right;     // the pad on that side holds another slab's particles, not wall ghosts
@@ -409,7 +410,7 @@ struct SweepArgs {
     double *vn, *un;        // fully-kicked outputs (iterate)
     const double *vh, *uh;  // half-kicked base state of i itself
     int *dirty;             // per-tile stamp: epoch of the last sweep that changed something in range
-    int *wl[2];             // work lists of tiles for the sweeps of even / odd epoch
+    int *wl[3];             // work lists of tiles, by sweep stamp mod 3
     Ctl *ctl;
     int pad, na;
     double m0, half_dt;
@@ -624,8 +625,8 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
                 if (jmin < A.pad) ta = 0;
                 for (int t = ta; t <= tb; t++) {
                     if (atomicMax(A.dirty + t, epoch) < epoch) {
-                        const int slot = atomicAdd(&A.ctl->nwork[(epoch + 1) & 1], 1);
-                        A.wl[(epoch + 1) & 1][slot] = t;
+                        const int slot = atomicAdd(&A.ctl->nwork[(epoch + 1) % 3], 1);
+                        A.wl[(epoch + 1) % 3][slot] = t;
                     }
                 }
             }
@@ -666,11 +667,14 @@ __global__ void __launch_bounds__(kTile) k_force_refine(SweepArgs A, int max_swe
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
     const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
-    int epoch = ctl->epoch_cur;   // stamp of the latest sweep, which filled wl[(epoch + 1) & 1]
+    int epoch = ctl->epoch_cur;   // stamp of the latest sweep, which filled wl[(epoch + 1) % 3]
     int used = ctl->sweeps_used;
+    int peak = 0;
     grid.sync();                  // everybody has read the hand-over words before block 0 rewrites them
+    // Three rotating lists make ONE grid-wide barrier per sweep enough: sweep e reads list e % 3, fills
+    // (e + 1) % 3 and clears (e + 2) % 3, which every CTA finished reading before the previous barrier.
     while (true) {
-        const int cur = (epoch + 1) & 1;
+        const int cur = (epoch + 1) % 3;
         const int nwork = *((volatile int *)&ctl->nwork[cur]);
         if (nwork == 0) break;
         if (used >= max_sweeps) {
@@ -679,8 +683,8 @@ __global__ void __launch_bounds__(kTile) k_force_refine(SweepArgs A, int max_swe
         }
         epoch++;
         used++;
-        if (blockIdx.x == 0 && threadIdx.x == 0) ctl->nwork[(epoch + 1) & 1] = 0;   // the list this sweep fills
-        grid.sync();
+        peak = max(peak, nwork);
+        if (blockIdx.x == 0 && threadIdx.x == 0) ctl->nwork[(epoch + 2) % 3] = 0;
         for (int w = blockIdx.x; w < nwork; w += gridDim.x) {
             const int tile = __ldcg(A.wl[cur] + w);
             bool changed;
@@ -689,6 +693,7 @@ __global__ void __launch_bounds__(kTile) k_force_refine(SweepArgs A, int max_swe
         }
         grid.sync();
     }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && peak > ctl->nwork_peak) ctl->nwork_peak = peak;
     if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->sweeps_used = used; ctl->epoch_cur = epoch; }
 }
 
@@ -958,7 +963,7 @@ struct SlabArgs {
     unsigned *idx;
     Rec2 *rec;
     int *dirty;
-    int *wl[2];
+    int *wl[3];
     Ctl *ctl;
     int pad, na, K;
     int side;        // -1: my left edge / my left pad, +1: right
@@ -1060,8 +1065,8 @@ __global__ void __launch_bounds__(1024) k_slab_unpack(SlabArgs A, int what, cons
         const int tb = A.side < 0 ? min(s_tile, ntiles - 1) : ntiles - 1;
         for (int t = ta + threadIdx.x; t <= tb; t += blockDim.x) {
             if (atomicMax(A.dirty + t, epoch) < epoch) {
-                const int slot = atomicAdd(&ctl->nwork[(epoch + 1) & 1], 1);
-                A.wl[(epoch + 1) & 1][slot] = t;
+                const int slot = atomicAdd(&ctl->nwork[(epoch + 1) % 3], 1);
+                A.wl[(epoch + 1) % 3][slot] = t;
             }
         }
         if (threadIdx.x == 0) ctl->halo_changed = 1;
@@ -1127,6 +1132,8 @@ __global__ void k_begin(Ctl *ctl, int clear_cand) {
     if (clear_cand) ctl->ncand = 0;
     ctl->nwork[0] = 0;
     ctl->nwork[1] = 0;
+    ctl->nwork[2] = 0;
+    ctl->nwork_peak = 0;
     ctl->halo_changed = 0;
     ctl->force_pairs = 0ull;
 }

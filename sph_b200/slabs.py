@@ -302,14 +302,67 @@ class SlabSimulation:
             r.close()
 
 
+class NativeSlabSimulation:
+    """One process per GPU; the whole protocol runs inside libsphb (sphb_slab_step: grouped
+    ncclSend/ncclRecv on the handle's stream, one host synchronisation per step).  Python only
+    distributes the NCCL unique id through the already initialised torch.distributed group."""
+
+    def __init__(self, rank_obj: SlabRank):
+        import torch
+        import torch.distributed as dist
+        self.ranks = [rank_obj]
+        r = rank_obj
+        self.stream = torch.cuda.Stream(device=r.device)
+        r.set_stream(self.stream.cuda_stream)
+        ident = [None]
+        if r.rank == 0:
+            buf = C.create_string_buffer(128)
+            r._check(r.L.sphb_nccl_unique_id(buf))
+            ident[0] = buf.raw
+        dist.broadcast_object_list(ident, src=0)
+        r._check(r.L.sphb_slab_comm_init(r.h, ident[0]))
+        self._torch = torch
+
+    def init_lattice(self):
+        r = self.ranks[0]
+        r._check(r.L.sphb_slab_init_particles(r.h))
+
+    def step(self, nsteps=1):
+        r = self.ranks[0]
+        r._check(r.L.sphb_slab_step(r.h, nsteps))
+
+    @property
+    def rounds_last(self):
+        r = self.ranks[0]
+        return r.L.sphb_slab_rounds_last(r.h)
+
+    def set_profiling(self, on=True):
+        self.ranks[0].set_profiling(on)
+
+    def phase_times(self, reset=False):
+        return self.ranks[0].phase_times(reset)
+
+    def counters(self):
+        return self.ranks[0].counters()
+
+    def fields(self):
+        return self.ranks[0].fields()
+
+    def close(self):
+        self.ranks[0].close()
+
+
 def make_simulation(config: Config, variable_h=True, fixed_h=0.2, device=-1, rank=0, world=1,
-                    halo_count=256, **kw):
+                    halo_count=256, native=True, **kw):
     """world == 1: one device-resident Simulation.  world > 1 (one process per GPU under
-    torch.distributed): this rank's slab."""
+    torch.distributed): this rank's slab, exchanging halos inside libsphb (native) or through
+    torch.distributed point-to-point calls."""
     if world == 1:
         return Simulation(config, variable_h=variable_h, fixed_h=fixed_h, device=device, **kw)
     r = SlabRank(config, rank, world, config.n_part, halo_count=halo_count, device=device,
                  variable_h=variable_h, fixed_h=fixed_h, **kw)
+    if native:
+        return NativeSlabSimulation(r)
     return SlabSimulation([r], DistTransport(r))
 
 

@@ -24,7 +24,8 @@ def main():
     cfg = Config(n_part=n, mass=4.0 / (n - 1), pressure_calc=1, t_i=0.005 * 100 / (n - 1))
     one = Simulation(cfg, device=local)
     one.init_lattice()
-    sim = make_simulation(cfg, device=local, rank=rank, world=world, halo_count=128)
+    native = os.environ.get("SLAB_NATIVE", "1") == "1"
+    sim = make_simulation(cfg, device=local, rank=rank, world=world, halo_count=128, native=native)
     sim.init_lattice()
     bad = 0
     for st in range(0, 7):
@@ -38,7 +39,8 @@ def main():
             na = r.i1 - r.i0
             same = np.array_equal(f1[r.i0:r.i1], f2[:na])
             print("rank %d step %d: slab [%d, %d) %s, rounds %d" % (rank, st, r.i0, r.i1,
-                                                                   "identical" if same else "DIFFERS", sim.rounds_last), flush=True)
+                                                                   "identical" if same else "DIFFERS", sim.rounds_last),
+                  "(native)" if native else "(torch.distributed)", flush=True)
             bad += 0 if same else 1
     t = torch.tensor([bad], device="cuda")
     dist.all_reduce(t)

@@ -136,8 +136,10 @@ def test_too_thin_a_halo_is_reported():
 
 
 @pytest.mark.gpu
-def test_slabs_over_nccl_match_single_handle():
-    """One process per GPU, NCCL send/recv (needs >= 2 GPUs on the box; skipped otherwise)."""
+@pytest.mark.parametrize("native", ["1", "0"])
+def test_slabs_over_nccl_match_single_handle(native):
+    """One process per GPU, NCCL send/recv (needs >= 2 GPUs on the box; skipped otherwise): the
+    exchange inside libsphb (native) and the torch.distributed one."""
     import subprocess
     import torch
     ngpu = torch.cuda.device_count()
@@ -147,6 +149,7 @@ def test_slabs_over_nccl_match_single_handle():
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
            os.path.join(ROOT, "tests", "dist_slab_check.py")]
-    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900,
+                         env=dict(os.environ, SLAB_NATIVE=native))
     assert res.returncode == 0, res.stdout[-3000:]
     assert "DIFFERS" not in res.stdout
