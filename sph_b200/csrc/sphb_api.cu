@@ -1211,6 +1211,8 @@ int sphb_get_counters(sphb_handle *H, sphb_counters *out) {
     { long long b = (long long)H->h_ctl->hmax_bits; memcpy(&out->h_max, &b, sizeof(double)); }
     out->launches = H->launches;
     out->force_pairs_mean = H->na ? (double)H->h_ctl->force_pairs / H->na : 0.0;
+    out->refine_tiles = H->h_ctl->tiles_swept;
+    out->refine_tile_evals = H->h_ctl->tile_evals;
     if (H->have_counts) {
         const int n = H->na;
         std::vector<int> nw((size_t)n + 2 * H->pad), nb((size_t)n + 2 * H->pad);

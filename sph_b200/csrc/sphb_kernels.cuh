@@ -52,6 +52,8 @@ struct Ctl {
     unsigned long long fallbacks;  // bisection fallbacks taken
     int nwork[3];                  // tiles in the work list of the sweep whose stamp is k mod 3
     int nwork_peak;                // largest work list of the current step (sizes the next step's refinement grid)
+    int tile_evals;                // tile evaluations (in-tile iterations included) of the current step's refinement
+    int tiles_swept;               // tiles taken from the work lists in the current step
     int sweeps_used;               // force sweeps the last step needed
     int epoch_cur;                 // stamp of the most recent force sweep (handed from launch to launch)
     int halo_left, halo_right;     // the pad on that side holds another slab's particles, not wall ghosts
@@ -107,6 +109,7 @@ struct __align__(64) Rec2 { Rec A, B; };   // new state (as seen once the sweep 
 
 constexpr int kDHalo = 64;    // density pass: x staged on each side of a tile
 constexpr int kFHalo = 32;    // force pass: neighbour state staged on each side of a tile
+constexpr int kLocalIters = 48;  // cap on the in-tile iterations of one refinement sweep
 
 // ------------------------------------------------------------------------------------
 // One evaluation of the two density-pass sums at trial smoothing length h over the sorted
@@ -576,33 +579,57 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
     __syncthreads();
 
     const int s = t0 + threadIdx.x;
+    const bool active = s < tend;
+    const int ks = s - wbase;
     bool changed = false;
     int npairs = 0;
-    if (s < tend) {
-        const int ks = s - wbase;
-        Own<ADIA> o;
-        const double vi = A.vh[s], ui = A.uh[s];
-        {
-            Rec ro;
-            ro.h = S.hc[0][ks].x; ro.c5 = S.hc[0][ks].y; ro.rho = S.rk[0][ks].x; ro.kap = S.rk[0][ks].y;
-            o.set(sx[ks], S.idx[ks], ro, vi, ui, A.Pstale[s]);
+    Own<ADIA> o;
+    double vi = 0.0, ui = 0.0;
+    if (active) {
+        vi = A.vh[s]; ui = A.uh[s];
+        Rec ro;
+        ro.h = S.hc[0][ks].x; ro.c5 = S.hc[0][ks].y; ro.rho = S.rk[0][ks].x; ro.kap = S.rk[0][ks].y;
+        o.set(sx[ks], S.idx[ks], ro, vi, ui, A.Pstale[s]);
+    }
+    const double reach = kRadius * Hb;
+    const double gsum = active ? A.F.gsum[s] : 0.0;
+    double a_sum = 0.0, e_sum = 0.0, vf = 0.0, uf = 0.0;
+    int jmin = s, jmax = s;
+    bool local_cap = false;
+    // A refinement sweep iterates the tile ON ITS SHARED-MEMORY IMAGE until nothing in it moves any
+    // more (the particles outside the tile keep their staged values): the chain of dependencies
+    // inside a tile then costs CTA barriers instead of grid-wide sweeps.
+#pragma unroll 1
+    for (int it = 0;; it++) {
+        bool moved = false;
+        if (active) {
+            a_sum = 0.0; e_sum = 0.0;
+            npairs = 1;   // self: its energy term is evaluated by the reference too (and is exactly 0)
+            force_side<SEL, ADIA, UM, FIRST, -1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmin);
+            force_side<SEL, ADIA, UM, FIRST, +1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmax);
+            if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
+            a_sum = fma(-o.PrRho, gsum, a_sum);               // - P_i/(rho_i^2 om_i) sum_j m_j gradW_ij(h_i)
+            // second half-kick, sph_simulation.cpp:105-106, operation by operation
+            vf = __dadd_rn(vi, __dmul_rn(a_sum, A.half_dt));
+            uf = __dadd_rn(ui, __dmul_rn(e_sum, A.half_dt));
+            if (!FIRST)
+                moved = (__double_as_longlong(vf) != __double_as_longlong(S.vA[ks])) ||
+                        (__double_as_longlong(uf) != __double_as_longlong(S.uA[ks]));
         }
-        const double reach = kRadius * Hb;
-        double a_sum = 0.0, e_sum = 0.0;
-        int jmin = s, jmax = s;
-        npairs = 1;   // self: its energy term is evaluated by the reference too (and is exactly 0)
-        force_side<SEL, ADIA, UM, FIRST, -1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmin);
-        force_side<SEL, ADIA, UM, FIRST, +1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmax);
-        if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
-        a_sum = fma(-o.PrRho, A.F.gsum[s], a_sum);        // - P_i/(rho_i^2 om_i) sum_j m_j gradW_ij(h_i)
+        if (FIRST) break;
+        if (!__syncthreads_or(moved)) break;      // also: everybody is done reading the image
+        if (moved) { S.vA[ks] = vf; S.uA[ks] = uf; }
+        if (threadIdx.x == 0) atomicAdd(&A.ctl->tile_evals, 1);
+        __syncthreads();
+        if (it >= kLocalIters) { local_cap = true; break; }
+    }
+    if (!FIRST && threadIdx.x == 0) { atomicAdd(&A.ctl->tile_evals, 1); atomicAdd(&A.ctl->tiles_swept, 1); }
+    if (active) {
         if (!A.kick) {
             A.a[s] = a_sum;
             A.du[s] = e_sum;
             A.Pout[s] = o.P;
         } else {
-            // second half-kick, sph_simulation.cpp:105-106, operation by operation
-            const double vf = __dadd_rn(vi, __dmul_rn(a_sum, A.half_dt));
-            const double uf = __dadd_rn(ui, __dmul_rn(e_sum, A.half_dt));
             if (FIRST) {
                 A.a[s] = a_sum; A.du[s] = e_sum; A.Pout[s] = o.P;
                 A.vn[s] = vf; A.un[s] = uf;
@@ -619,11 +646,13 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
                 if (changed) { __stcg(A.vn + s, vf); __stcg(A.un + s, uf); }
             }
             if (changed && SEL == SEL_INDEX) {
-                // every tile holding a particle within reach must be looked at again next sweep
+                // every OTHER tile holding a particle within reach must be looked at again next sweep;
+                // this one too after the first sweep, or if its local iteration was cut short
                 const int ntiles = (A.na + kTile - 1) / kTile;
                 int ta = max((jmin - A.pad) / kTile, 0), tb = min((jmax - A.pad) / kTile, ntiles - 1);
                 if (jmin < A.pad) ta = 0;
                 for (int t = ta; t <= tb; t++) {
+                    if (t == tile && !FIRST && !local_cap) continue;
                     if (atomicMax(A.dirty + t, epoch) < epoch) {
                         const int slot = atomicAdd(&A.ctl->nwork[(epoch + 1) % 3], 1);
                         A.wl[(epoch + 1) % 3][slot] = t;
@@ -1134,6 +1163,8 @@ __global__ void k_begin(Ctl *ctl, int clear_cand) {
     ctl->nwork[1] = 0;
     ctl->nwork[2] = 0;
     ctl->nwork_peak = 0;
+    ctl->tile_evals = 0;
+    ctl->tiles_swept = 0;
     ctl->halo_changed = 0;
     ctl->force_pairs = 0ull;
 }
