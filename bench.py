@@ -210,7 +210,7 @@ def run_ours(args, name, n, pc, varh):
     cfg = Config(n_part=n, mass=kw["mass"], pressure_calc=pc, t_i=kw["t_i"])
     from sph_b200.slabs import make_simulation   # 1 rank: a plain Simulation; >1: this rank's x-slab
     sim = make_simulation(cfg, variable_h=varh, fixed_h=kw["constant_h"], device=local, rank=rank, world=world,
-                          halo_count=args.halo, native=not args.torch_exchange)
+                          halo_count=args.halo, native=not args.torch_exchange, sweep_rel_tol=args.sweep_tol)
     if world > 1:
         stream = sim.stream                      # handle, halo messages and NCCL calls share it
     else:
@@ -353,7 +353,8 @@ def run_ours(args, name, n, pc, varh):
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": name, "n_particles": n, "pressure_calc": "adiabatic" if pc == 1 else "isothermal",
                        "smoothing_length": "variable (Newton/bisection per particle)" if varh else "fixed, 5 spacings",
-                       "order": "reference (index-ordered in-place sweep, exact)", "sweeps_per_step": sweeps_mean,
+                       "order": ("reference (index-ordered in-place sweep, bitwise fixed point)" if args.sweep_tol == 0 else
+                                 "reference (index-ordered in-place sweep, converged to %.1e relative)" % args.sweep_tol), "sweeps_per_step": sweeps_mean,
                        "parallelism": ("x-slabs x%d, %d-particle halos over ncclSend/ncclRecv, %d ITERATE exchanges in the last step"
                                        % (world, args.halo, rounds_last)) if world > 1 else "single GPU",
                        "l2": "state arrays (%.1f GB) larger than L2, no flush needed" % (n * 8 * 20 / 1e9)},
@@ -371,6 +372,8 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--n", type=int, default=0, help="override the particle count of the workload")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sweep-tol", type=float, default=0.0,
+                    help="0 (default): the ordered sweep is iterated to its bitwise fixed point; > 0: relative tolerance")
     ap.add_argument("--torch-exchange", action="store_true",
                     help="x-slab runs: drive the halo exchange from Python (torch.distributed) instead of inside libsphb")
     ap.add_argument("--halo", type=int, default=256, help="particles exchanged per slab edge (x-slab runs)")

@@ -61,7 +61,11 @@ typedef struct sphb_options {
     int pad_capacity;    /* max ghost (or halo) particles per side (default 4096) */
     int capacity;        /* max alive particles; 0 = config.n_part */
     int sort_every_step; /* 1: radix-sort every step; 0: only when the order check fails */
-    int reserved[8];
+    double sweep_rel_tol; /* SPHB_ORDER_REFERENCE: 0 (default) iterates the ordered sweep to its BITWISE fixed point, i.e. the
+                             reference's sequential result exactly; > 0 stops once no kicked v, u moves by more than this
+                             relative amount (v against max(|v|, c_s)): bounded deviation, far fewer sweeps when every
+                             particle's kick is non-zero */
+    int reserved[6];
 } sphb_options;
 
 typedef struct sphb_counters {

@@ -35,7 +35,8 @@ class SphbConfig(C.Structure):
 class SphbOptions(C.Structure):
     _fields_ = [("variable_h", C.c_int), ("fixed_h", C.c_double), ("order", C.c_int),
                 ("max_sweeps", C.c_int), ("device", C.c_int), ("pad_capacity", C.c_int),
-                ("capacity", C.c_int), ("sort_every_step", C.c_int), ("reserved", C.c_int * 8)]
+                ("capacity", C.c_int), ("sort_every_step", C.c_int), ("sweep_rel_tol", C.c_double),
+                ("reserved", C.c_int * 6)]
 
 
 class SphbCounters(C.Structure):
@@ -95,7 +96,8 @@ class SphbError(RuntimeError):
 
 
 def lib_path() -> str:
-    return os.path.join(_HERE, "libsphb.so")
+    # SPHB_LIB: an alternative build of the same library (kernel experiments, tools/)
+    return os.environ.get("SPHB_LIB") or os.path.join(_HERE, "libsphb.so")
 
 
 def declared_symbols() -> list:
@@ -186,7 +188,8 @@ class Simulation:
     """One device-resident simulation (an sphb_handle)."""
 
     def __init__(self, config: Config, variable_h=True, fixed_h=0.2, order=ORDER_REFERENCE,
-                 max_sweeps=64, device=-1, pad_capacity=4096, capacity=0, sort_every_step=False):
+                 max_sweeps=64, device=-1, pad_capacity=4096, capacity=0, sort_every_step=False,
+                 sweep_rel_tol=0.0):
         self.L = load_library()
         self.config = config
         opt = SphbOptions()
@@ -199,6 +202,7 @@ class Simulation:
         opt.pad_capacity = pad_capacity
         opt.capacity = capacity
         opt.sort_every_step = int(sort_every_step)
+        opt.sweep_rel_tol = float(sweep_rel_tol)
         self.h = C.c_void_p()
         cfg = config.to_c()
         rc = self.L.sphb_create(C.byref(cfg), C.byref(opt), C.byref(self.h))

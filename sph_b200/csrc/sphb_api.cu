@@ -316,7 +316,7 @@ SweepArgs sweep_args(sphb_handle *H) {
     A.F.rec = H->rec; A.F.gsum = H->gsum;
     A.a = H->a; A.du = H->du; A.dirty = H->dirty; A.wl[0] = H->wl0; A.wl[1] = H->wl1; A.wl[2] = H->wl2; A.ctl = H->d_ctl;
     A.pad = H->pad; A.na = H->na; A.m0 = H->m0; A.half_dt = H->cfg.t_i / 2;
-    A.epoch = H->epoch; A.kick = 1;
+    A.epoch = H->epoch; A.kick = 1; A.tol = H->opt.sweep_rel_tol;
     A.vn = H->vn; A.un = H->un;
     return A;
 }
@@ -657,7 +657,7 @@ int sphb_create(const sphb_config *cfg, const sphb_options *opt_in, sphb_handle 
     sphb_options opt;
     if (opt_in) opt = *opt_in; else sphb_default_options(&opt);
     if (cfg->n_part < 1 || cfg->n_ghost < 0 || cfg->n_ghost > cfg->n_part) { H->err = "bad n_part / n_ghost"; return SPHB_ERR_INVALID; }
-    if (opt.pad_capacity < 1 || opt.max_sweeps < 1) { H->err = "bad options"; return SPHB_ERR_INVALID; }
+    if (opt.pad_capacity < 1 || opt.max_sweeps < 1 || !(opt.sweep_rel_tol >= 0.0)) { H->err = "bad options"; return SPHB_ERR_INVALID; }
     if (cfg->pressure_calc != SPHB_ISOTHERMAL && cfg->pressure_calc != SPHB_ADIABATIC) {
         H->err = "Unknown pressure calculation mode!";   // calculators.cpp:80-82
         return SPHB_ERR_INVALID;

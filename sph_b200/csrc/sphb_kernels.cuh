@@ -419,6 +419,7 @@ struct SweepArgs {
     double m0, half_dt;
     int epoch;              // stamp of this sweep
     int kick;               // 0: t = 0 semantics (no kick, calculators only)
+    double tol;             // 0: iterate to the bitwise fixed point; > 0: until every change is below tol (relative)
 };
 
 // per-thread invariants of one force evaluation
@@ -543,10 +544,15 @@ __device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &
             if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
         }
     }
-    if ((j < lo || j >= hi) && (DIR < 0 ? A.ctl->halo_left : A.ctl->halo_right)) raise(A.ctl, E_HALO, wbase + ks);
     jend = j - DIR;
     a_sum = DIR > 0 ? (a_sum + accA) : (a_sum - accA);
     e_sum = DIR > 0 ? (e_sum - accE) : (e_sum + accE);
+}
+
+// Did a kicked value move?  tol == 0: any bit; else by more than tol relative to `scale`.
+__device__ __forceinline__ bool moved_by(double a, double b, double tol, double scale) {
+    if (tol == 0.0) return __double_as_longlong(a) != __double_as_longlong(b);
+    return fabs(a - b) > tol * scale;
 }
 
 // Evaluate one tile: stage, compute a, du/dt (and the kick), store.  Returns through
@@ -581,76 +587,103 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
     const int s = t0 + threadIdx.x;
     const bool active = s < tend;
     const int ks = s - wbase;
-    bool changed = false;
-    int npairs = 0;
-    Own<ADIA> o;
-    double vi = 0.0, ui = 0.0;
-    if (active) {
-        vi = A.vh[s]; ui = A.uh[s];
-        Rec ro;
-        ro.h = S.hc[0][ks].x; ro.c5 = S.hc[0][ks].y; ro.rho = S.rk[0][ks].x; ro.kap = S.rk[0][ks].y;
-        o.set(sx[ks], S.idx[ks], ro, vi, ui, A.Pstale[s]);
-    }
     const double reach = kRadius * Hb;
-    const double gsum = active ? A.F.gsum[s] : 0.0;
-    double a_sum = 0.0, e_sum = 0.0, vf = 0.0, uf = 0.0;
-    int jmin = s, jmax = s;
-    bool local_cap = false;
-    // A refinement sweep iterates the tile ON ITS SHARED-MEMORY IMAGE until nothing in it moves any
-    // more (the particles outside the tile keep their staged values): the chain of dependencies
-    // inside a tile then costs CTA barriers instead of grid-wide sweeps.
-#pragma unroll 1
-    for (int it = 0;; it++) {
-        bool moved = false;
-        if (active) {
-            a_sum = 0.0; e_sum = 0.0;
-            npairs = 1;   // self: its energy term is evaluated by the reference too (and is exactly 0)
-            force_side<SEL, ADIA, UM, FIRST, -1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmin);
-            force_side<SEL, ADIA, UM, FIRST, +1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmax);
-            if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
-            a_sum = fma(-o.PrRho, gsum, a_sum);               // - P_i/(rho_i^2 om_i) sum_j m_j gradW_ij(h_i)
-            // second half-kick, sph_simulation.cpp:105-106, operation by operation
-            vf = __dadd_rn(vi, __dmul_rn(a_sum, A.half_dt));
-            uf = __dadd_rn(ui, __dmul_rn(e_sum, A.half_dt));
-            if (!FIRST)
-                moved = (__double_as_longlong(vf) != __double_as_longlong(S.vA[ks])) ||
-                        (__double_as_longlong(uf) != __double_as_longlong(S.uA[ks]));
-        }
-        if (FIRST) break;
-        if (!__syncthreads_or(moved)) break;      // also: everybody is done reading the image
-        if (moved) { S.vA[ks] = vf; S.uA[ks] = uf; }
-        if (threadIdx.x == 0) atomicAdd(&A.ctl->tile_evals, 1);
-        __syncthreads();
-        if (it >= kLocalIters) { local_cap = true; break; }
+    // On a slab edge the scan must end INSIDE the halo.  x is sorted, so it is enough to look at the own
+    // particle next to each pad: if its scan stops before the end of the array, everybody's does.
+    if (threadIdx.x == 0) {
+        if (tile == 0 && A.ctl->halo_left && A.F.x[A.pad] - A.F.x[lo] < reach) raise(A.ctl, E_HALO, A.pad);
+        if (tend == A.pad + A.na && A.ctl->halo_right && A.F.x[hi - 1] - A.F.x[tend - 1] < reach)
+            raise(A.ctl, E_HALO, tend - 1);
     }
-    if (!FIRST && threadIdx.x == 0) { atomicAdd(&A.ctl->tile_evals, 1); atomicAdd(&A.ctl->tiles_swept, 1); }
-    if (active) {
-        if (!A.kick) {
+    bool changed = false, local_cap = false;
+    int npairs = 0, jmin = s, jmax = s;
+
+    if constexpr (FIRST) {
+        // sweep 1 of a step (or the kick-less t = 0 pass): everybody is seen half-kicked, one evaluation
+        if (active) {
+            Own<ADIA> o;
+            const double vi = A.vh[s], ui = A.uh[s];
+            {
+                Rec ro;
+                ro.h = S.hc[0][ks].x; ro.c5 = S.hc[0][ks].y; ro.rho = S.rk[0][ks].x; ro.kap = S.rk[0][ks].y;
+                o.set(sx[ks], S.idx[ks], ro, vi, ui, A.Pstale[s]);
+            }
+            double a_sum = 0.0, e_sum = 0.0;
+            npairs = 1;   // self: its energy term is evaluated by the reference too (and is exactly 0)
+            force_side<SEL, ADIA, UM, true, -1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmin);
+            force_side<SEL, ADIA, UM, true, +1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmax);
+            if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
+            a_sum = fma(-o.PrRho, A.F.gsum[s], a_sum);        // - P_i/(rho_i^2 om_i) sum_j m_j gradW_ij(h_i)
             A.a[s] = a_sum;
             A.du[s] = e_sum;
             A.Pout[s] = o.P;
-        } else {
-            if (FIRST) {
-                A.a[s] = a_sum; A.du[s] = e_sum; A.Pout[s] = o.P;
+            if (A.kick) {
+                // second half-kick, sph_simulation.cpp:105-106, operation by operation
+                const double vf = __dadd_rn(vi, __dmul_rn(a_sum, A.half_dt));
+                const double uf = __dadd_rn(ui, __dmul_rn(e_sum, A.half_dt));
                 A.vn[s] = vf; A.un[s] = uf;
                 // later-index neighbours used (vh, uh) as their guess for this particle
-                changed = (__double_as_longlong(vf) != __double_as_longlong(vi)) ||
-                          (__double_as_longlong(uf) != __double_as_longlong(ui));
-            } else {
-                const double vo = __ldcg(A.vn + s), uo = __ldcg(A.un + s);
-                changed = (__double_as_longlong(vf) != __double_as_longlong(vo)) ||
-                          (__double_as_longlong(uf) != __double_as_longlong(uo));
-                // a, du feed the next step's first kick: they must come from THIS (possibly final)
-                // evaluation even when the kicked values round to what is already stored
-                A.a[s] = a_sum; A.du[s] = e_sum;
-                if (changed) { __stcg(A.vn + s, vf); __stcg(A.un + s, uf); }
+                changed = moved_by(vf, vi, A.tol, fmax(fabs(vi), o.c_ec)) || moved_by(uf, ui, A.tol, fabs(ui));
             }
-            if (changed && SEL == SEL_INDEX) {
-                // every OTHER tile holding a particle within reach must be looked at again next sweep;
-                // this one too after the first sweep, or if its local iteration was cut short
+        }
+    } else {
+        // A refinement sweep iterates the tile ON ITS SHARED-MEMORY IMAGE until nothing in it moves any
+        // more (the particles outside the tile keep their staged values): the chain of dependencies
+        // inside a tile then costs CTA barriers instead of grid-wide sweeps.
+        Own<ADIA> o;
+        double vi = 0.0, ui = 0.0, gsum = 0.0, vscale = 1.0;
+        if (active) {
+            vi = A.vh[s]; ui = A.uh[s]; gsum = A.F.gsum[s];
+            Rec ro;
+            ro.h = S.hc[0][ks].x; ro.c5 = S.hc[0][ks].y; ro.rho = S.rk[0][ks].x; ro.kap = S.rk[0][ks].y;
+            o.set(sx[ks], S.idx[ks], ro, vi, ui, A.Pstale[s]);
+            vscale = fmax(fabs(vi), o.c_ec);   // velocities pass through zero: judge them against max(|v|, c_s)
+        }
+        double a_sum = 0.0, e_sum = 0.0, vf = 0.0, uf = 0.0;
+#pragma unroll 1
+        for (int it = 0;; it++) {
+            bool moved = false;
+            if (active) {
+                a_sum = 0.0; e_sum = 0.0;
+                force_side<SEL, ADIA, UM, false, -1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmin);
+                force_side<SEL, ADIA, UM, false, +1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmax);
+                if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
+                a_sum = fma(-o.PrRho, gsum, a_sum);
+                vf = __dadd_rn(vi, __dmul_rn(a_sum, A.half_dt));
+                uf = __dadd_rn(ui, __dmul_rn(e_sum, A.half_dt));
+                moved = moved_by(vf, S.vA[ks], A.tol, vscale) || moved_by(uf, S.uA[ks], A.tol, fabs(ui));
+            }
+            if (!__syncthreads_or(moved)) break;      // also: everybody is done reading the image
+            if (moved) { S.vA[ks] = vf; S.uA[ks] = uf; }
+            if (threadIdx.x == 0) atomicAdd(&A.ctl->tile_evals, 1);
+            __syncthreads();
+            if (it >= kLocalIters) { local_cap = true; break; }
+        }
+        if (threadIdx.x == 0) { atomicAdd(&A.ctl->tile_evals, 1); atomicAdd(&A.ctl->tiles_swept, 1); }
+        if (active) {
+            const double vo = __ldcg(A.vn + s), uo = __ldcg(A.un + s);
+            changed = moved_by(vf, vo, A.tol, vscale) || moved_by(uf, uo, A.tol, fabs(ui));
+            // a, du feed the next step's first kick: they must come from THIS (possibly final)
+            // evaluation even when the kicked values round to what is already stored
+            A.a[s] = a_sum; A.du[s] = e_sum;
+            if (changed) { __stcg(A.vn + s, vf); __stcg(A.un + s, uf); }
+        }
+    }
+    // Every OTHER tile holding a particle within reach of a changed one must be looked at again next
+    // sweep; this tile too after the first sweep, or if its local iteration was cut short.  One thread
+    // queues for the whole tile (a step in which every particle moves would otherwise drown in atomics).
+    if (SEL == SEL_INDEX && A.kick) {
+        __shared__ int s_jmin, s_jmax;
+        if (__syncthreads_or(changed)) {
+            if (threadIdx.x == 0) { s_jmin = 0x7fffffff; s_jmax = -1; }
+            __syncthreads();
+            if (changed) { atomicMin(&s_jmin, jmin); atomicMax(&s_jmax, jmax); }
+            __syncthreads();
+            if (threadIdx.x == 0) {
                 const int ntiles = (A.na + kTile - 1) / kTile;
-                int ta = max((jmin - A.pad) / kTile, 0), tb = min((jmax - A.pad) / kTile, ntiles - 1);
-                if (jmin < A.pad) ta = 0;
+                int ta = max((s_jmin - A.pad) / kTile, 0);
+                const int tb = min((s_jmax - A.pad) / kTile, ntiles - 1);
+                if (s_jmin < A.pad) ta = 0;
                 for (int t = ta; t <= tb; t++) {
                     if (t == tile && !FIRST && !local_cap) continue;
                     if (atomicMax(A.dirty + t, epoch) < epoch) {
@@ -668,7 +701,10 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
 // First force sweep of a step over every alive particle (also the only one for the
 // jacobi order and for the kick-less t = 0 pass).
 template <int SEL, bool ADIA, bool UM>
-__global__ void __launch_bounds__(kTile, 4) k_force_first(SweepArgs A) {
+#ifndef SPHB_EXP_FIRST_BLOCKS
+#define SPHB_EXP_FIRST_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(kTile, SPHB_EXP_FIRST_BLOCKS) k_force_first(SweepArgs A) {
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
     const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
