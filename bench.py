@@ -290,8 +290,16 @@ def run_ours(args, name, n, pc, varh):
     step_prof_ms = sum(v[0] for v in phases.values()) / prof_steps
     dom = max((("density", d_ms, bytes_density), ("force_first", f_ms, bytes_force)), key=lambda t: t[1])
     achieved = n_local * dom[2] / (dom[1] * 1e-3) / 1e9 if dom[1] > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": "k_density" if dom[0] == "density" else "k_force_first",
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    kname = "k_density" if dom[0] == "density" else "k_force_first"
+    traffic = None
+    try:   # dram bytes per launch from the committed ncu --set full capture, scaled to this launch's particles
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic_r01.json")))
+        traffic = (tr[kname]["dram_bytes_read"] + tr[kname]["dram_bytes_write"]) / tr["n_particles"] * n_local
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": kname,
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                "traffic_source": "profiles/traffic_r01.json: ncu dram__bytes_read+write per launch at N = 16 Mi, scaled per particle",
                 "peak_source": peak_src, "bytes_per_particle": dom[2], "launch_ms": dom[1],
                 "step_b_ns_bytes_per_particle": b_ns,
                 "step_frac_b_ns": value / world * b_ns / 1e9 / peak,
