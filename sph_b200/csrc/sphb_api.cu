@@ -63,6 +63,9 @@ struct sphb_handle {
     double *msg_send[3][2] = {}, *msg_recv[3][2] = {};
     int *d_flags = nullptr, *h_flags = nullptr;
     int fixed_rounds = 1, rounds_last = 0;
+    cudaStream_t comm_stream = nullptr;          // BASE / RECORDS exchanges run here, beside the interior tiles
+    cudaEvent_t ev_kick = nullptr, ev_base = nullptr, ev_edge = nullptr, ev_rec = nullptr;
+    int part = 0;                                // 0: all tiles, 1: interior tiles only, 2: edge tiles only
     bool uniform_mass = true;
     double m0 = 0.0;
     bool have_counts = false;
@@ -261,7 +264,17 @@ int launch_density(sphb_handle *H, int root_alive, int root_ghosts, int check_ol
     A.cnt = H->cnt; A.ctl = H->d_ctl; A.pad = H->pad; A.na = H->na;
     A.limit = H->cfg.limit; A.hfac = H->cfg.h_factor; A.m0 = H->m0;
     A.root_ghosts = root_ghosts; A.root_alive = root_alive; A.check_old = check_old;
-    const int grid = nblk(H->na + 2 * H->pad, kTile);
+    int grid = nblk(H->na + 2 * H->pad, kTile);
+    A.tile_split = grid; A.tile_skip = 0;
+    if (H->part) {
+        // edge = every tile that can see a pad: the pads themselves plus K + one tile of own particles
+        const int e = H->K + kTile;
+        const int tl = std::min(grid, nblk(H->pad + e, kTile));
+        const int tr = std::max(tl, (H->pad + H->na - e) / kTile);
+        if (H->part == 1) { A.tile_split = 0; A.tile_skip = tl; grid = tr - tl; }
+        else { A.tile_split = tl; A.tile_skip = tr - tl; grid = grid - (tr - tl); }
+        if (grid <= 0) return SPHB_OK;
+    }
     const bool varh = H->opt.variable_h != 0;
     if (varh && H->uniform_mass) k_density<true, true><<<grid, kTile, 0, H->stream>>>(A);
     else if (varh) k_density<true, false><<<grid, kTile, 0, H->stream>>>(A);
@@ -269,14 +282,21 @@ int launch_density(sphb_handle *H, int root_alive, int root_ghosts, int check_ol
     else k_density<false, false><<<grid, kTile, 0, H->stream>>>(A);
     H->launches++;
     CK(cudaGetLastError());
-    H->launches++;
     if (root_alive || root_ghosts) H->have_counts = true;
     return SPHB_OK;
 }
 
 template <int SEL>
-int launch_first_sel(sphb_handle *H, const SweepArgs &A) {
-    const int grid = nblk(H->na, kTile);
+int launch_first_sel(sphb_handle *H, SweepArgs A) {
+    int grid = nblk(H->na, kTile);
+    A.tile_split = grid; A.tile_skip = 0;
+    if (H->part) {
+        const int te = std::min(grid, nblk(H->K + kTile, kTile));
+        const int tr = std::max(te, grid - te);
+        if (H->part == 1) { A.tile_split = 0; A.tile_skip = te; grid = tr - te; }
+        else { A.tile_split = te; A.tile_skip = tr - te; grid = grid - (tr - te); }
+        if (grid <= 0) return SPHB_OK;
+    }
     const bool adia = H->cfg.pressure_calc == SPHB_ADIABATIC;
     if (adia && H->uniform_mass) k_force_first<SEL, true, true><<<grid, kTile, 0, H->stream>>>(A);
     else if (adia) k_force_first<SEL, true, false><<<grid, kTile, 0, H->stream>>>(A);
@@ -600,12 +620,38 @@ int native_exchange(sphb_handle *H, int what) {
     return SPHB_OK;
 }
 
-// everything of a step after the drift, up to the agreed flags (the step's one host synchronisation)
+// run fn with the handle's stream switched to the communication stream
+template <class F>
+int on_comm_stream(sphb_handle *H, F fn) {
+    cudaStream_t keep = H->stream;
+    H->stream = H->comm_stream;
+    const int rc = fn();
+    H->stream = keep;
+    return rc;
+}
+
+// Everything of a step after the drift, up to the agreed flags (the step's one host synchronisation).
+// The BASE and RECORDS exchanges run on a second stream beside the interior tiles of the density and
+// force kernels; only the tiles that can see a pad ("edge": K + one tile of particles at each end)
+// wait for them.
 int native_attempt(sphb_handle *H, int *rounds) {
-    TRY(native_exchange(H, MSG_BASE));
-    TRY(step_density(H));
-    TRY(native_exchange(H, MSG_RECORDS));
-    TRY(step_force_first(H));
+    CK(cudaEventRecord(H->ev_kick, H->stream));
+    CK(cudaStreamWaitEvent(H->comm_stream, H->ev_kick, 0));
+    TRY(on_comm_stream(H, [&] { return native_exchange(H, MSG_BASE); }));
+    CK(cudaEventRecord(H->ev_base, H->comm_stream));
+    H->part = 1; TRY(launch_density(H, 1, 0, 1, H->Pn));            // interior tiles
+    CK(cudaStreamWaitEvent(H->stream, H->ev_base, 0));
+    H->part = 2; TRY(launch_density(H, 1, 0, 1, H->Pn));            // edge tiles, halo in place
+    H->part = 0;
+    phase_end(H, 3);
+    CK(cudaEventRecord(H->ev_edge, H->stream));
+    CK(cudaStreamWaitEvent(H->comm_stream, H->ev_edge, 0));
+    TRY(on_comm_stream(H, [&] { return native_exchange(H, MSG_RECORDS); }));
+    CK(cudaEventRecord(H->ev_rec, H->comm_stream));
+    H->part = 1; TRY(step_force_first(H));
+    CK(cudaStreamWaitEvent(H->stream, H->ev_rec, 0));
+    H->part = 2; TRY(step_force_first(H));
+    H->part = 0;
     TRY(step_refine(H));
     for (int r = 0; r < H->fixed_rounds; r++) {
         TRY(native_exchange(H, MSG_ITERATE));
@@ -735,6 +781,8 @@ void sphb_destroy(sphb_handle *H) {
     for (void *p : ptrs) if (p) cudaFree(p);
     if (H->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(H->comm);
     for (int w = 0; w < 3; w++) for (int k = 0; k < 2; k++) { if (H->msg_send[w][k]) cudaFree(H->msg_send[w][k]); if (H->msg_recv[w][k]) cudaFree(H->msg_recv[w][k]); }
+    if (H->comm_stream) cudaStreamDestroy(H->comm_stream);
+    for (cudaEvent_t e : {H->ev_kick, H->ev_base, H->ev_edge, H->ev_rec}) if (e) cudaEventDestroy(e);
     if (H->d_flags) cudaFree(H->d_flags);
     if (H->h_flags) cudaFreeHost(H->h_flags);
     if (H->h_ctl) cudaFreeHost(H->h_ctl);
@@ -1136,6 +1184,9 @@ int sphb_slab_comm_init(sphb_handle *H, const void *unique_id128) {
         }
     TRY(dalloc(H, &H->d_flags, 4));
     CK(cudaMallocHost((void **)&H->h_flags, 4 * sizeof(int)));
+    CK(cudaStreamCreateWithFlags(&H->comm_stream, cudaStreamNonBlocking));
+    for (cudaEvent_t *e : {&H->ev_kick, &H->ev_base, &H->ev_edge, &H->ev_rec})
+        CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     CK(cudaStreamSynchronize(H->stream));
     return SPHB_OK;
 }
