@@ -276,10 +276,16 @@ int launch_density(sphb_handle *H, int root_alive, int root_ghosts, int check_ol
         if (grid <= 0) return SPHB_OK;
     }
     const bool varh = H->opt.variable_h != 0;
-    if (varh && H->uniform_mass) k_density<true, true><<<grid, kTile, 0, H->stream>>>(A);
-    else if (varh) k_density<true, false><<<grid, kTile, 0, H->stream>>>(A);
-    else if (H->uniform_mass) k_density<false, true><<<grid, kTile, 0, H->stream>>>(A);
-    else k_density<false, false><<<grid, kTile, 0, H->stream>>>(A);
+#define SPHB_DENS(V, U)                                                              \
+    do {                                                                             \
+        if (H->slab) k_density<V, U, true><<<grid, kTile, 0, H->stream>>>(A);        \
+        else k_density<V, U, false><<<grid, kTile, 0, H->stream>>>(A);               \
+    } while (0)
+    if (varh && H->uniform_mass) SPHB_DENS(true, true);
+    else if (varh) SPHB_DENS(true, false);
+    else if (H->uniform_mass) SPHB_DENS(false, true);
+    else SPHB_DENS(false, false);
+#undef SPHB_DENS
     H->launches++;
     CK(cudaGetLastError());
     if (root_alive || root_ghosts) H->have_counts = true;
@@ -298,10 +304,16 @@ int launch_first_sel(sphb_handle *H, SweepArgs A) {
         if (grid <= 0) return SPHB_OK;
     }
     const bool adia = H->cfg.pressure_calc == SPHB_ADIABATIC;
-    if (adia && H->uniform_mass) k_force_first<SEL, true, true><<<grid, kTile, 0, H->stream>>>(A);
-    else if (adia) k_force_first<SEL, true, false><<<grid, kTile, 0, H->stream>>>(A);
-    else if (H->uniform_mass) k_force_first<SEL, false, true><<<grid, kTile, 0, H->stream>>>(A);
-    else k_force_first<SEL, false, false><<<grid, kTile, 0, H->stream>>>(A);
+#define SPHB_FIRST(AD, U)                                                                        \
+    do {                                                                                         \
+        if (H->part) k_force_first<SEL, AD, U, true><<<grid, kTile, 0, H->stream>>>(A);          \
+        else k_force_first<SEL, AD, U, false><<<grid, kTile, 0, H->stream>>>(A);                 \
+    } while (0)
+    if (adia && H->uniform_mass) SPHB_FIRST(true, true);
+    else if (adia) SPHB_FIRST(true, false);
+    else if (H->uniform_mass) SPHB_FIRST(false, true);
+    else SPHB_FIRST(false, false);
+#undef SPHB_FIRST
     H->launches++;
     CK(cudaGetLastError());
     return SPHB_OK;
@@ -1370,8 +1382,9 @@ int sphb_density_static(const double *d_x, const double *d_h, const double *d_rh
     A.limit = limit; A.hfac = h_factor; A.m0 = mass;
     A.root_ghosts = 0; A.root_alive = 1; A.check_old = 0;
     const int grid = nblk(n, kTile);
-    if (variable_h) k_density<true, true><<<grid, kTile, 0, st>>>(A);
-    else k_density<false, true><<<grid, kTile, 0, st>>>(A);
+    A.tile_split = grid; A.tile_skip = 0;
+    if (variable_h) k_density<true, true, false><<<grid, kTile, 0, st>>>(A);
+    else k_density<false, true, false><<<grid, kTile, 0, st>>>(A);
     CK(cudaGetLastError());
     Ctl host_ctl;   // pageable stack memory: the copy allocates nothing
     CK(cudaMemcpyAsync(&host_ctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));

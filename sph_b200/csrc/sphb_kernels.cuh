@@ -236,13 +236,15 @@ struct DensityArgs {
 // (calculators.cpp:45) and omega_new; the first evaluation is at the old h, so its
 // derivative sum gives omega_stale = calc_omega(old h, old rho) at the new positions.
 // With f(h) = m_i sigma Sw / h^5 - m_i hf / h and f'(h) = -sigma Sg / h^6 + m_i hf / h^2.
-template <bool VARH, bool UM>
+// SLAB: pads may hold another slab's particles and the launch may cover a subset of the tiles
+template <bool VARH, bool UM, bool SLAB>
 __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
     __shared__ double sxs[kTile + 2 * kDHalo + 2];
     double *sx = sxs + 1;
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
-    const int t0 = ((int)blockIdx.x < A.tile_split ? (int)blockIdx.x : (int)blockIdx.x + A.tile_skip) * kTile;   // tiles of [0, pad + na + pad)
+    const int t0 = (!SLAB ? (int)blockIdx.x
+                          : ((int)blockIdx.x < A.tile_split ? (int)blockIdx.x : (int)blockIdx.x + A.tile_skip)) * kTile;   // tiles of [0, pad + na + pad)
     if (t0 >= hi || t0 + kTile <= lo) return;
     const int wbase = max(t0 - kDHalo, lo);
     const int wn = min(t0 + kTile + kDHalo, hi) - wbase;
@@ -253,7 +255,7 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
     const int s = t0 + threadIdx.x;
     double hloc = 0.0;
     // pad slots that hold another slab's particles get everything from their owner
-    const bool halo_slot = (s < A.pad && ctl->halo_left) || (s >= A.pad + A.na && ctl->halo_right);
+    const bool halo_slot = SLAB && ((s < A.pad && ctl->halo_left) || (s >= A.pad + A.na && ctl->halo_right));
     if (s >= lo && s < hi && !halo_slot) {
         const bool is_pad = (s < A.pad) || (s >= A.pad + A.na);
         const bool do_root = VARH && (is_pad ? A.root_ghosts : A.root_alive);
@@ -267,7 +269,7 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
         double Sw, Sg, Sgr = 0.0;
 #define SPHB_EVAL(H_, F_, DF_, DSUM_)                                                           \
     {                                                                                           \
-        density_sums<UM>(ctl, !is_pad, sx, wbase, wn, A.x, A.m, s, lo, hi, xi, (H_), Sw, Sg, Sgr, cnt); \
+        density_sums<UM>(ctl, SLAB && !is_pad, sx, wbase, wn, A.x, A.m, s, lo, hi, xi, (H_), Sw, Sg, Sgr, cnt); \
         const double ih_ = 1.0 / (H_), ih2_ = ih_ * ih_, ih4_ = ih2_ * ih2_;                    \
         const double rho_ = mi * (kSigma * (Sw * (ih4_ * ih_)));                                \
         F_ = rho_ - mi * A.hfac * ih_;                                                          \
@@ -546,9 +548,33 @@ __device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &
             if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
         }
     }
+    if ((j < lo || j >= hi) && (DIR < 0 ? A.ctl->halo_left : A.ctl->halo_right)) raise(A.ctl, E_HALO, wbase + ks);
     jend = j - DIR;
     a_sum = DIR > 0 ? (a_sum + accA) : (a_sum - accA);
     e_sum = DIR > 0 ? (e_sum - accE) : (e_sum + accE);
+}
+
+// Every tile holding a particle within reach of a changed one must be looked at again next sweep
+// (all but `skip_tile`).  The converged lanes of a warp queue together: one lane does the atomics for
+// all of them (a step in which every particle moves would otherwise drown in atomics).
+__device__ __forceinline__ void queue_dependents(const SweepArgs &A, bool changed, int jmin, int jmax, int epoch,
+                                                 int skip_tile) {
+    const unsigned act = __activemask();
+    if (!__ballot_sync(act, changed)) return;
+    const int wmin = __reduce_min_sync(act, changed ? jmin : 0x7fffffff);
+    const int wmax = __reduce_max_sync(act, changed ? jmax : -1);
+    if ((threadIdx.x & 31) != __ffs(act) - 1) return;
+    const int ntiles = (A.na + kTile - 1) / kTile;
+    int ta = max((wmin - A.pad) / kTile, 0);
+    const int tb = min((wmax - A.pad) / kTile, ntiles - 1);
+    if (wmin < A.pad) ta = 0;
+    for (int t = ta; t <= tb; t++) {
+        if (t == skip_tile) continue;
+        if (atomicMax(A.dirty + t, epoch) < epoch) {
+            const int slot = atomicAdd(&A.ctl->nwork[(epoch + 1) % 3], 1);
+            A.wl[(epoch + 1) % 3][slot] = t;
+        }
+    }
 }
 
 // Did a kicked value move?  tol == 0: any bit; else by more than tol relative to `scale`.
@@ -587,51 +613,53 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
     __syncthreads();
 
     const int s = t0 + threadIdx.x;
-    const bool active = s < tend;
-    const int ks = s - wbase;
-    const double reach = kRadius * Hb;
-    // On a slab edge the scan must end INSIDE the halo.  x is sorted, so it is enough to look at the own
-    // particle next to each pad: if its scan stops before the end of the array, everybody's does.
-    if (threadIdx.x == 0) {
-        if (tile == 0 && A.ctl->halo_left && A.F.x[A.pad] - A.F.x[lo] < reach) raise(A.ctl, E_HALO, A.pad);
-        if (tend == A.pad + A.na && A.ctl->halo_right && A.F.x[hi - 1] - A.F.x[tend - 1] < reach)
-            raise(A.ctl, E_HALO, tend - 1);
-    }
-    bool changed = false, local_cap = false;
-    int npairs = 0, jmin = s, jmax = s;
+    bool changed = false;
+    int npairs = 0;
 
     if constexpr (FIRST) {
-        // sweep 1 of a step (or the kick-less t = 0 pass): everybody is seen half-kicked, one evaluation
-        if (active) {
+        // sweep 1 of a step (or the kick-less t = 0 pass): everybody is seen half-kicked, one evaluation.
+        // (Everything is scoped inside this branch on purpose: hoisting ks / reach out of it costs the
+        // 64-register kernel 100 bytes of extra spill traffic per thread and 10 % of its speed.)
+        if (s < tend) {
+            const int ks2 = s - wbase;
             Own<ADIA> o;
             const double vi = A.vh[s], ui = A.uh[s];
             {
                 Rec ro;
-                ro.h = S.hc[0][ks].x; ro.c5 = S.hc[0][ks].y; ro.rho = S.rk[0][ks].x; ro.kap = S.rk[0][ks].y;
-                o.set(sx[ks], S.idx[ks], ro, vi, ui, A.Pstale[s]);
+                ro.h = S.hc[0][ks2].x; ro.c5 = S.hc[0][ks2].y; ro.rho = S.rk[0][ks2].x; ro.kap = S.rk[0][ks2].y;
+                o.set(sx[ks2], S.idx[ks2], ro, vi, ui, A.Pstale[s]);
             }
+            const double reach2 = kRadius * Hb;
             double a_sum = 0.0, e_sum = 0.0;
+            int jmin = s, jmax = s;
             npairs = 1;   // self: its energy term is evaluated by the reference too (and is exactly 0)
-            force_side<SEL, ADIA, UM, true, -1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmin);
-            force_side<SEL, ADIA, UM, true, +1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmax);
+            force_side<SEL, ADIA, UM, true, -1>(A, S, o, ks2, wbase, wn, lo, hi, reach2, a_sum, e_sum, npairs, jmin);
+            force_side<SEL, ADIA, UM, true, +1>(A, S, o, ks2, wbase, wn, lo, hi, reach2, a_sum, e_sum, npairs, jmax);
             if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
             a_sum = fma(-o.PrRho, A.F.gsum[s], a_sum);        // - P_i/(rho_i^2 om_i) sum_j m_j gradW_ij(h_i)
-            A.a[s] = a_sum;
-            A.du[s] = e_sum;
-            A.Pout[s] = o.P;
-            if (A.kick) {
+            if (!A.kick) {
+                A.a[s] = a_sum;
+                A.du[s] = e_sum;
+                A.Pout[s] = o.P;
+            } else {
                 // second half-kick, sph_simulation.cpp:105-106, operation by operation
                 const double vf = __dadd_rn(vi, __dmul_rn(a_sum, A.half_dt));
                 const double uf = __dadd_rn(ui, __dmul_rn(e_sum, A.half_dt));
+                A.a[s] = a_sum; A.du[s] = e_sum; A.Pout[s] = o.P;
                 A.vn[s] = vf; A.un[s] = uf;
                 // later-index neighbours used (vh, uh) as their guess for this particle
                 changed = moved_by(vf, vi, A.tol, fmax(fabs(vi), o.c_ec)) || moved_by(uf, ui, A.tol, fabs(ui));
+                if (SEL == SEL_INDEX) queue_dependents(A, changed, jmin, jmax, epoch, -1);
             }
         }
     } else {
         // A refinement sweep iterates the tile ON ITS SHARED-MEMORY IMAGE until nothing in it moves any
         // more (the particles outside the tile keep their staged values): the chain of dependencies
         // inside a tile then costs CTA barriers instead of grid-wide sweeps.
+        const bool active = s < tend;
+        const int ks = s - wbase;
+        const double reach = kRadius * Hb;
+        bool local_cap = false;
         Own<ADIA> o;
         double vi = 0.0, ui = 0.0, gsum = 0.0, vscale = 1.0;
         if (active) {
@@ -642,6 +670,7 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
             vscale = fmax(fabs(vi), o.c_ec);   // velocities pass through zero: judge them against max(|v|, c_s)
         }
         double a_sum = 0.0, e_sum = 0.0, vf = 0.0, uf = 0.0;
+        int jmin = s, jmax = s;
 #pragma unroll 1
         for (int it = 0;; it++) {
             bool moved = false;
@@ -669,31 +698,8 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
             // evaluation even when the kicked values round to what is already stored
             A.a[s] = a_sum; A.du[s] = e_sum;
             if (changed) { __stcg(A.vn + s, vf); __stcg(A.un + s, uf); }
-        }
-    }
-    // Every OTHER tile holding a particle within reach of a changed one must be looked at again next
-    // sweep; this tile too after the first sweep, or if its local iteration was cut short.  One thread
-    // queues for the whole tile (a step in which every particle moves would otherwise drown in atomics).
-    if (SEL == SEL_INDEX && A.kick) {
-        __shared__ int s_jmin, s_jmax;
-        if (__syncthreads_or(changed)) {
-            if (threadIdx.x == 0) { s_jmin = 0x7fffffff; s_jmax = -1; }
-            __syncthreads();
-            if (changed) { atomicMin(&s_jmin, jmin); atomicMax(&s_jmax, jmax); }
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                const int ntiles = (A.na + kTile - 1) / kTile;
-                int ta = max((s_jmin - A.pad) / kTile, 0);
-                const int tb = min((s_jmax - A.pad) / kTile, ntiles - 1);
-                if (s_jmin < A.pad) ta = 0;
-                for (int t = ta; t <= tb; t++) {
-                    if (t == tile && !FIRST && !local_cap) continue;
-                    if (atomicMax(A.dirty + t, epoch) < epoch) {
-                        const int slot = atomicAdd(&A.ctl->nwork[(epoch + 1) % 3], 1);
-                        A.wl[(epoch + 1) % 3][slot] = t;
-                    }
-                }
-            }
+            // this tile itself only if its local iteration was cut short
+            if (SEL == SEL_INDEX) queue_dependents(A, changed, jmin, jmax, epoch, local_cap ? -1 : tile);
         }
     }
     changed_any = changed;
@@ -702,18 +708,16 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
 
 // First force sweep of a step over every alive particle (also the only one for the
 // jacobi order and for the kick-less t = 0 pass).
-template <int SEL, bool ADIA, bool UM>
-#ifndef SPHB_EXP_FIRST_BLOCKS
-#define SPHB_EXP_FIRST_BLOCKS 4
-#endif
-__global__ void __launch_bounds__(kTile, SPHB_EXP_FIRST_BLOCKS) k_force_first(SweepArgs A) {
+template <int SEL, bool ADIA, bool UM, bool MAPPED>
+__global__ void __launch_bounds__(kTile, 4) k_force_first(SweepArgs A) {
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
     const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
     bool changed;
     int npairs;
     if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->epoch_cur = A.epoch; ctl->sweeps_used = 1; }
-    const int tile = (int)blockIdx.x < A.tile_split ? (int)blockIdx.x : (int)blockIdx.x + A.tile_skip;
+    const int tile = !MAPPED ? (int)blockIdx.x
+                             : ((int)blockIdx.x < A.tile_split ? (int)blockIdx.x : (int)blockIdx.x + A.tile_skip);
     force_tile<SEL, ADIA, UM, true>(A, tile, lo, hi, Hb, A.epoch, changed, npairs);
     // pair statistics for the roofline accounting (one atomic per warp)
     for (int o = 16; o > 0; o >>= 1) npairs += __shfl_xor_sync(0xffffffffu, npairs, o);

@@ -1,0 +1,391 @@
+#!/usr/bin/env python
+"""bench.py — particle-steps/s of the per-timestep particle loop (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+A "step" is one pass of SPHSimulation::step_forward (sph_simulation.cpp:55-108) over the whole
+particle set: kick-drift, ghosts, fused density + variable-h root-find + omega, fused
+acceleration + du/dt with the reference's index-ordered sweep, second kick.  Inputs are the
+synthetic colliding-stream lattice of setup.cpp:145-185 scaled to N,
+generated on the device by sphb_init_lattice.
+
+One JSON line on stdout (rank 0):
+  value      whole-job particle-steps/s, state resident in HBM, CUDA events on the launching stream
+  e2e        same metric through the host-facing C-ABI route with HOST buffers every step:
+             sphb_upload (pinned AoS Particle[] -> device) + sphb_step(1) + sphb_download
+  roofline   dominant kernel (fused density/root-find/omega): algorithmic bytes per launch ÷ its
+             CUDA-event duration, against MEASURED_PEAKS.json's HBM copy bandwidth
+  cpu_baseline  the plain-C O(N k) port of the reference (oracle/) timed on one host core on a
+             bounded sample of the same workload
+--impl reference times the reference's own code (oracle/_ref, built from /root/reference by
+oracle/Makefile) on the host cores instead; nothing of sph_b200 runs on that arm.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "particle_steps_per_sec"
+UNIT = "particle-steps/s"
+
+# name -> (N, pressure_calc, variable_h); h for fixed-h runs is 5 lattice spacings
+WORKLOADS = {
+    "colliding_streams_adiabatic_varh_n64m": (64 * 1024 * 1024, 1, True),     # BASELINE configs[3], the target line
+    "colliding_streams_adiabatic_varh_n16m": (16 * 1024 * 1024, 1, True),     # configs[2]
+    "colliding_streams_isothermal_fixedh_n1m": (1024 * 1024, 0, False),       # configs[1]
+    "colliding_streams_adiabatic_varh_n256m": (256 * 1024 * 1024, 1, True),   # configs[4]
+    "colliding_streams_adiabatic_varh_n1m": (1024 * 1024, 1, True),
+}
+DEFAULT_WORKLOAD = "colliding_streams_adiabatic_varh_n64m"
+
+
+def workload_kwargs(n, pc, varh):
+    return dict(n_part=n, mass=4.0 / (n - 1), pressure_calc=pc, limit=2.0, v_0=1.0, h_factor=2.0,
+                t_i=0.005 * 100 / (n - 1), variable_h=varh, constant_h=0.2 * 100 / (n - 1))
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._pump, daemon=True)
+            self.thr.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------
+# CPU legs (the only places bench.py may execute oracle/)
+
+def cpu_port_baseline(pc, varh, sample_n=400_001, steps=3):
+    """The O(N k) plain-C port (oracle/sph_oracle.c), one thread, same generator at sample_n."""
+    from oracle.sph_oracle import Oracle
+    kw = workload_kwargs(sample_n, pc, varh)
+    o = Oracle(**kw)
+    t0 = time.perf_counter()
+    o.step(steps)
+    dt = time.perf_counter() - t0
+    o.close()
+    return {"value": sample_n * steps / dt, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": "same lattice generator at N=%d, %d steps after t=0 set-up, %.1f s; O(N k) port of the "
+                      "reference (the literal reference is O(N^3) and cannot run at this N)" % (sample_n, steps, dt)}
+
+
+def _ref_worker(args):
+    n, pc, varh, steps, warm = args
+    from oracle import ref_literal
+    kw = workload_kwargs(n, pc, varh)
+    r = ref_literal.RefLiteral(flavour="ofast", **kw)
+    if warm:
+        r.step(warm)
+    t0 = time.perf_counter()
+    r.step(steps)
+    dt = time.perf_counter() - t0
+    r.close()
+    return dt
+
+
+def run_reference(args, name, n_full, pc, varh):
+    """The reference's own sources (oracle/_ref, -Ofast like its Makefile) on the host cores.  It is
+    single-threaded and O(N^3) per step in variable-h mode (calculators.cpp:117), so a bounded sample of
+    the workload is the same lattice at small N; one independent replica per host core is run so that
+    every core the box has is used.  Falls back to the O(N k) port where oracle/_ref is absent."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import ref_literal
+    steps, warm = max(1, args.steps), max(0, args.warmup)
+    cores = os.cpu_count() or 1
+    if ref_literal.available(varh, "ofast"):
+        import multiprocessing as mp
+        n_s = 401 if varh else 3201          # ~0.3 s / step / core either way
+        steps_s, warm_s = min(steps, 6), min(warm, 1)
+        with mp.get_context("spawn").Pool(cores) as pool:
+            t0 = time.perf_counter()
+            dts = pool.map(_ref_worker, [(n_s, pc, varh, steps_s, warm_s)] * cores)
+            wall = time.perf_counter() - t0
+        dt = max(dts)
+        value = cores * n_s * steps_s / dt
+        kind = "reference"
+        sample = ("reference sources compiled unmodified (-Ofast), %d independent replicas (one per core) of the same "
+                  "lattice at N=%d, %d steps each, slowest replica %.2f s (wall %.1f s); the reference step is O(N^%d) so "
+                  "its rate falls as N grows" % (cores, n_s, steps_s, dt, wall, 3 if varh else 2))
+        ms = dt / steps_s * 1e3
+        steps_out = steps_s
+    else:
+        b = cpu_port_baseline(pc, varh)
+        value, kind, sample, cores = b["value"], "port", b["sample"], 1
+        ms, steps_out = None, 3
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": steps_out, "warmup": warm, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": name, "n_particles": n_full},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------
+
+def run_ours(args, name, n, pc, varh):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from sph_b200 import PARTICLE_DTYPE, Config, Simulation
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — libsphb has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("bench.py --gpus %d must be launched under torch.distributed.run" % args.gpus)
+
+    kw = workload_kwargs(n, pc, varh)
+    cfg = Config(n_part=n, mass=kw["mass"], pressure_calc=pc, t_i=kw["t_i"])
+    from sph_b200.slabs import make_simulation   # 1 rank: a plain Simulation; >1: this rank's x-slab
+    sim = make_simulation(cfg, variable_h=varh, fixed_h=kw["constant_h"], device=local, rank=rank, world=world,
+                          halo_count=args.halo, native=not args.torch_exchange)
+    if world > 1:
+        stream = sim.stream                      # handle, halo messages and NCCL calls share it
+    else:
+        stream = torch.cuda.Stream()
+        sim.set_stream(stream.cuda_stream)
+    sim.init_lattice()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        sim.step(1)
+    barrier()
+    launches0 = sim.counters().launches
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    with torch.cuda.stream(stream):
+        ev0.record(stream)
+        for _ in range(args.steps):
+            sim.step(1)
+        ev1.record(stream)
+    barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if rank == 0 else None
+    c = sim.counters()
+    launches = c.launches - launches0
+    if world > 1:
+        t = torch.tensor([ms_total], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+        lt = torch.tensor([launches], device="cuda", dtype=torch.int64)
+        dist.all_reduce(lt, op=dist.ReduceOp.SUM)
+        launches = int(lt.item())
+    ms_step = ms_total / args.steps
+    value = n * args.steps / (ms_total * 1e-3)
+    sweeps_mean = (c.sweeps_total / max(c.steps, 1))
+
+    # ---- per-kernel durations (CUDA events on the launching stream, live, after the timed region)
+    prof_steps = min(args.steps, 10)
+    sim.set_profiling(True)
+    sim.phase_times(reset=True)
+    for _ in range(prof_steps):
+        sim.step(1)
+    barrier()
+    phases = sim.phase_times(reset=True)
+    sim.set_profiling(False)
+    c2 = sim.counters()
+    n_local = c2.n_alive
+    if world > 1:     # statistics below are per rank; take the busiest phase times over ranks
+        for k in list(phases):
+            t = torch.tensor([phases[k][0]], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            phases[k] = (float(t.item()), phases[k][1])
+    hist = c2.newton_hist
+    tot = max(sum(hist), 1)
+    newton_mean = sum(k * v for k, v in enumerate(hist)) / tot if varh else 0.0
+    nbr_rho = c2.nbr_mean
+    nbr_f = max(c2.force_pairs_mean - 1.0, 0.0)
+    passes = (1.0 + newton_mean) if varh else 1.0
+    # algorithmic bytes per particle: density kernel reads x,h,rho and writes
+    # h,rho,omega_new,omega_stale (56 B) + 8 B (x_j) per neighbour per pass of the root-find
+    bytes_density = (56.0 if varh else 24.0) + 8.0 * passes * nbr_rho
+    rec = 56.0 if varh else 40.0
+    bytes_force = (124.0 if pc == 1 else 92.0) + rec * nbr_f
+    bytes_kick = 64.0
+    b_ns = bytes_kick + bytes_density + bytes_force
+    peak, peak_src = measured_peaks()
+    d_ms = phases["density"][0] / max(phases["density"][1], 1)
+    f_ms = phases["force_first"][0] / max(phases["force_first"][1], 1)
+    r_ms = phases["force_refine"][0] / max(phases["force_refine"][1], 1)
+    k_ms = phases["kick_drift"][0] / max(phases["kick_drift"][1], 1)
+    step_prof_ms = sum(v[0] for v in phases.values()) / prof_steps
+    dom = max((("density", d_ms, bytes_density), ("force_first", f_ms, bytes_force)), key=lambda t: t[1])
+    achieved = n_local * dom[2] / (dom[1] * 1e-3) / 1e9 if dom[1] > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": "k_density" if dom[0] == "density" else "k_force_first",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "bytes_per_particle": dom[2], "launch_ms": dom[1],
+                "step_b_ns_bytes_per_particle": b_ns,
+                "step_frac_b_ns": value / world * b_ns / 1e9 / peak,
+                "step_frac_compulsory_244B": value / world * (244.0 if varh else 156.0) / 1e9 / peak,
+                "phase_ms": {"kick_drift": k_ms, "density": d_ms, "force_first": f_ms, "force_refine": r_ms,
+                             "sort": phases["sort"][0] / prof_steps, "ghosts": phases["ghosts"][0] / prof_steps,
+                             "step_sum": step_prof_ms},
+                "kernel_share_of_step": dom[1] / step_prof_ms if step_prof_ms > 0 else None}
+
+    # ---- end to end through the C-ABI with HOST buffers, every step: upload + step + download
+    e2e = None
+    if True:
+        # every rank moves ITS particles (the whole set on one GPU, its slab otherwise) through host memory
+        e2e_steps = max(1, min(args.steps, 3))
+        hs = sim if world == 1 else sim.ranks[0]     # the object that owns this rank's handle
+        n_loc = n_local
+        nbuf = n_loc + 2 * 4096
+        host = torch.empty(nbuf * PARTICLE_DTYPE.itemsize, dtype=torch.uint8, pin_memory=True)
+        rec_arr = host.numpy().view(PARTICLE_DTYPE)
+        out, ng = hs.download(rec_arr)
+        barrier()
+        h2d = d2h = 0
+        with torch.cuda.stream(stream):
+            ev0.record(stream)
+            for _ in range(e2e_steps):
+                npart = len(out)
+                hs.upload(rec_arr[:npart], ng)
+                h2d += npart * PARTICLE_DTYPE.itemsize
+                sim.step(1)
+                out, ng = hs.download(rec_arr)
+                d2h += len(out) * PARTICLE_DTYPE.itemsize
+            ev1.record(stream)
+        barrier()
+        e2e_ms = ev0.elapsed_time(ev1)
+        if world > 1:
+            t = torch.tensor([e2e_ms, float(h2d), float(d2h)], device="cuda", dtype=torch.float64)
+            tmax = t.clone()
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            e2e_ms, h2d, d2h = float(tmax[0].item()), int(t[1].item()), int(t[2].item())
+        e2e = {"value": n * e2e_steps / (e2e_ms * 1e-3), "unit": UNIT, "steps": e2e_steps,
+               "h2d_bytes_per_step": h2d // e2e_steps, "d2h_bytes_per_step": d2h // e2e_steps,
+               "ms_per_step": e2e_ms / e2e_steps,
+               "route": "sphb_upload(pinned Particle[]) + sphb_step(1) + sphb_download(Particle[]), all ranks"}
+    rounds_last = getattr(sim, 'rounds_last', 0)
+    sim.close()
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_port_baseline(pc, varh)
+
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return 0
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": name, "n_particles": n, "pressure_calc": "adiabatic" if pc == 1 else "isothermal",
+                       "smoothing_length": "variable (Newton/bisection per particle)" if varh else "fixed, 5 spacings",
+                       "order": "reference (index-ordered in-place sweep, exact)", "sweeps_per_step": sweeps_mean,
+                       "parallelism": ("x-slabs x%d, %d-particle halos over ncclSend/ncclRecv, %d ITERATE exchanges in the last step"
+                                       % (world, args.halo, rounds_last)) if world > 1 else "single GPU",
+                       "l2": "state arrays (%.1f GB) larger than L2, no flush needed" % (n * 8 * 20 / 1e9)},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--n", type=int, default=0, help="override the particle count of the workload")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--torch-exchange", action="store_true",
+                    help="x-slab runs: drive the halo exchange from Python (torch.distributed) instead of inside libsphb")
+    ap.add_argument("--halo", type=int, default=256, help="particles exchanged per slab edge (x-slab runs)")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    n, pc, varh = WORKLOADS[args.workload]
+    name = args.workload
+    if args.n:
+        n = args.n
+        name += "(n=%d)" % n
+    if args.impl == "reference":
+        return run_reference(args, name, n, pc, varh)
+    return run_ours(args, name, n, pc, varh)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,1335 @@
+// sphb_api.cu — host side of libsphb.so: the C-ABI of include/sphb.h over the kernels
+// in sphb_kernels.cuh.  No CPU fallback exists: without a usable CUDA device every entry
+// point fails with SPHB_ERR_NO_DEVICE / SPHB_ERR_CUDA.
+#include <cub/device/device_radix_sort.cuh>
+#include <dlfcn.h>
+#include <nccl.h>   // types only: the library is opened at run time (sphb_slab_comm_init)
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/sphb.h"
+#include "sphb_kernels.cuh"
+
+using namespace sphb;
+
+static_assert(sizeof(sphb_particle) == 88, "sphb_particle must match the reference Particle");
+static_assert(sizeof(sphb_config) == 64, "sphb_config must match the reference Config");
+
+struct sphb_handle {
+    sphb_config cfg;
+    sphb_options opt;
+    int device = 0;
+    int num_sms = 0;
+    cudaStream_t stream = nullptr, own_stream = nullptr;
+    int pad = 0, cap_alive = 0, total = 0, cand_cap = 0;
+    int na = 0;
+    // state (current): positions, velocity, energy, derivatives, h, rho, stored pressure, mass
+    double *x = nullptr, *v = nullptr, *u = nullptr, *a = nullptr, *du = nullptr, *h = nullptr,
+           *rho = nullptr, *P = nullptr, *m = nullptr;
+    // per-step work arrays
+    double *xalt = nullptr, *vh = nullptr, *uh = nullptr, *vn = nullptr, *un = nullptr, *hn = nullptr,
+           *rhon = nullptr, *omn = nullptr, *oms = nullptr, *Pn = nullptr, *tmp = nullptr, *an = nullptr,
+           *dun = nullptr;   // acc, du_dt of the step in flight (swapped in by step_finish)
+    unsigned *idx = nullptr, *idx_alt = nullptr;
+    int *slot_id = nullptr, *cnt = nullptr, *dirty = nullptr, *cand = nullptr, *gorder = nullptr,
+        *perm = nullptr, *iota = nullptr, *wl0 = nullptr, *wl1 = nullptr, *wl2 = nullptr;
+    int refine_peak = 0;      // largest refinement work list of the previous step
+    Rec2 *rec = nullptr;      // force-pass records written by the density pass
+    double *gsum = nullptr;   // own-h gradient sums written by the density pass
+    // ghost staging (2*pad each)
+    double *gx = nullptr, *gv = nullptr, *gu = nullptr, *ga = nullptr, *gdu = nullptr, *gh = nullptr,
+           *grho = nullptr, *gP = nullptr, *gm = nullptr;
+    unsigned *gkey = nullptr;
+    Ctl *d_ctl = nullptr;
+    Ctl *h_ctl = nullptr;  // pinned
+    void *cub_tmp = nullptr;
+    size_t cub_bytes = 0;
+    AosRec *d_aos = nullptr;
+    size_t aos_cap = 0;
+    int *d_newton = nullptr, *d_nbr = nullptr;  // index-ordered count outputs (lazy)
+    bool ghost_in_half = false;   // ghosts' v,u live in the pads of vh/uh (after a step)
+    // x-slab decomposition (sphb_slab_*): this handle owns global indices [idx_base, idx_base + na)
+    bool slab = false, halo_l = false, halo_r = false;
+    int rank = 0, world = 1, K = 0;
+    long long idx_base = 0, n_global = 0;
+    // native exchange (sphb_slab_comm_init): NCCL communicator, message buffers [what][side], agreed flags
+    ncclComm_t comm = nullptr;
+    double *msg_send[3][2] = {}, *msg_recv[3][2] = {};
+    int *d_flags = nullptr, *h_flags = nullptr;
+    int fixed_rounds = 1, rounds_last = 0;
+    bool uniform_mass = true;
+    double m0 = 0.0;
+    bool have_counts = false;
+    long long steps = 0, sweeps_total = 0, sorts = 0;
+    unsigned long long fallbacks_committed = 0;   // bisection fallbacks of finished steps (a repeated attempt restarts from it)
+    int sweeps_last = 0;
+    int epoch = 8;
+    int refine_grid = 0;
+    long long launches = 0;
+    bool profiling = false;
+    cudaEvent_t ev[SPHB_PHASES + 1] = {};
+    double phase_ms[SPHB_PHASES] = {};
+    long long phase_n[SPHB_PHASES] = {};
+    bool phase_hit[SPHB_PHASES] = {};
+    std::string err;
+};
+
+namespace {
+
+#define CK(call)                                                                              \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess) {                                                              \
+            char b_[512];                                                                     \
+            snprintf(b_, sizeof b_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_),   \
+                     __FILE__, __LINE__);                                                     \
+            H->err = b_;                                                                      \
+            return SPHB_ERR_CUDA;                                                             \
+        }                                                                                     \
+    } while (0)
+
+#define TRY(expr)                 \
+    do {                          \
+        int rc_ = (expr);         \
+        if (rc_ != SPHB_OK) return rc_; \
+    } while (0)
+
+inline int nblk(int n, int b) { return (n + b - 1) / b; }
+
+const char *err_text(int code) {
+    switch (code) {
+        case SPHB_ERR_CAPACITY: return "more ghost particles than pad_capacity allows";
+        case SPHB_ERR_NEGATIVE_H: return "Root-finding returned negative smoothing length";
+        case SPHB_ERR_LOW_DENSITY: return "Particle had density less than epsilon!";
+        case SPHB_ERR_GHOST_ZERO_H: return "Ghost particle initialization: Particle had zero smoothing length!";
+        case SPHB_ERR_ZERO_DERIVATIVE: return "newton: derivative is zero";
+        case SPHB_ERR_NOT_FINITE: return "root-finding: function value is not finite";
+        case SPHB_ERR_NO_BRACKET: return "bisection: endpoints do not straddle y=0";
+        case SPHB_ERR_NOT_CONVERGED: return "ordered sweep did not converge within max_sweeps";
+        case SPHB_ERR_UNSORTED: return "x-order invariant violated";
+        case SPHB_ERR_HALO: return "x-slab halo thinner than the kernel support (raise halo_count)";
+        default: return "error";
+    }
+}
+
+template <class T>
+int dalloc(sphb_handle *H, T **p, size_t n) {
+    CK(cudaMalloc((void **)p, sizeof(T) * std::max<size_t>(n, 1)));
+    CK(cudaMemsetAsync(*p, 0, sizeof(T) * std::max<size_t>(n, 1), H->stream));
+    return SPHB_OK;
+}
+
+// Copy the control block to the host (one small D2H + stream sync) and turn a device
+// error word into a status.
+int read_ctl(sphb_handle *H) {
+    CK(cudaMemcpyAsync(H->h_ctl, H->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaStreamSynchronize(H->stream));
+    if (H->h_ctl->err_code != 0) {
+        char b[256];
+        snprintf(b, sizeof b, "%s (sorted slot %d)", err_text(H->h_ctl->err_code), H->h_ctl->err_particle);
+        H->err = b;
+        int code = H->h_ctl->err_code;
+        // clear so that the handle stays usable after the caller has seen the error
+        CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, 2 * sizeof(int), H->stream));
+        return code;
+    }
+    return SPHB_OK;
+}
+
+// ghosts made at the walls (pads that hold a neighbouring slab's particles do not count)
+int wall_ghosts(const sphb_handle *H) {
+    return (H->halo_l ? 0 : H->h_ctl->GL) + (H->halo_r ? 0 : H->h_ctl->GR);
+}
+
+void phase_begin(sphb_handle *H) {
+    if (H->profiling) cudaEventRecord(H->ev[0], H->stream);
+}
+// records the end of phase p; phases of one step are recorded back to back
+void phase_end(sphb_handle *H, int p) {
+    if (!H->profiling) return;
+    cudaEventRecord(H->ev[p + 1], H->stream);
+    H->phase_hit[p] = true;
+}
+void phase_collect(sphb_handle *H) {
+    if (!H->profiling) return;
+    cudaEvent_t prev = H->ev[0];
+    for (int p = 0; p < SPHB_PHASES; p++) {
+        if (!H->phase_hit[p]) continue;
+        float ms = 0.f;
+        cudaEventSynchronize(H->ev[p + 1]);
+        if (cudaEventElapsedTime(&ms, prev, H->ev[p + 1]) == cudaSuccess) {
+            H->phase_ms[p] += ms;
+            H->phase_n[p]++;
+        }
+        prev = H->ev[p + 1];
+        H->phase_hit[p] = false;
+    }
+}
+
+int launch_begin(sphb_handle *H, int clear_cand) {
+    k_begin<<<1, 1, 0, H->stream>>>(H->d_ctl, clear_cand);
+    H->launches++;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
+// kick + drift + ghost selection + order check (do_kick = 1), or selection + check only
+int launch_kick(sphb_handle *H, int do_kick) {
+    KickArgs A;
+    A.x = H->x; A.xo = H->xalt; A.v = H->v; A.u = H->u; A.a = H->a; A.du = H->du; A.h = H->h;
+    A.vh = H->vh; A.uh = H->uh; A.cand = H->cand; A.ctl = H->d_ctl;
+    A.pad = H->pad; A.na = H->na; A.cand_cap = H->cand_cap;
+    A.dt = H->cfg.t_i; A.half_dt = H->cfg.t_i / 2; A.limit = H->cfg.limit;
+    A.do_kick = do_kick;
+    if (H->na > 0) {
+        k_kick_drift<<<nblk(H->na, kTile), kTile, 0, H->stream>>>(A);
+        H->launches++;
+        CK(cudaGetLastError());
+    }
+    if (do_kick) std::swap(H->x, H->xalt);
+    return SPHB_OK;
+}
+
+int gather_f64(sphb_handle *H, double *&arr) {
+    k_gather_f64<<<nblk(H->na, 256), 256, 0, H->stream>>>(arr, H->tmp, H->perm, H->pad, H->na);
+    H->launches++;
+    CK(cudaGetLastError());
+    std::swap(arr, H->tmp);
+    return SPHB_OK;
+}
+
+// Radix-sort the alive block by x (CUB DeviceRadixSort on the FP64 keys with the slot
+// number as payload) and permute the listed arrays.  `full` = every state array (upload
+// path); otherwise only what is live between the drift and the density pass.
+int sort_alive(sphb_handle *H, bool full) {
+    if (H->na <= 1) return SPHB_OK;
+    k_iota<<<nblk(H->na, 256), 256, 0, H->stream>>>(H->iota, H->na);
+    H->launches++;
+    CK(cudaGetLastError());
+    size_t bytes = H->cub_bytes;
+    CK(cub::DeviceRadixSort::SortPairs(H->cub_tmp, bytes, H->x + H->pad, H->tmp + H->pad, H->iota, H->perm,
+                                       H->na, 0, 64, H->stream));
+    std::swap(H->x, H->tmp);   // sorted keys are the new positions
+    if (full) {
+        TRY(gather_f64(H, H->v)); TRY(gather_f64(H, H->u)); TRY(gather_f64(H, H->a)); TRY(gather_f64(H, H->du));
+    } else {
+        TRY(gather_f64(H, H->vh)); TRY(gather_f64(H, H->uh));
+        // a, du of the alive block are rewritten by the force pass, but the ghost copies made
+        // right after this sort take them from their source's slot (ghost_particles.cpp:53,111)
+        TRY(gather_f64(H, H->a)); TRY(gather_f64(H, H->du));
+    }
+    TRY(gather_f64(H, H->h)); TRY(gather_f64(H, H->rho)); TRY(gather_f64(H, H->P)); TRY(gather_f64(H, H->m));
+    k_gather_u32<<<nblk(H->na, 256), 256, 0, H->stream>>>(H->idx, H->idx_alt, H->perm, H->pad, H->na);
+    H->launches++;
+    CK(cudaGetLastError());
+    std::swap(H->idx, H->idx_alt);
+    H->sorts++;
+    return SPHB_OK;
+}
+
+// Place ghosts into the pads. from_alive: mirror the selected candidates out of (vs,us);
+// otherwise the staging arrays were filled by the upload.  Ghost v,u go to the pads of (vd,ud).
+int launch_ghost_build(sphb_handle *H, int from_alive, int nstaged, double *vs, double *us, double *vd, double *ud,
+                       bool into_next = false) {
+    GhostArgs G;
+    G.ad = into_next ? H->an : H->a; G.dud = into_next ? H->dun : H->du;
+    G.x = H->x; G.vd = vd; G.ud = ud; G.a = H->a; G.du = H->du; G.h = H->h; G.rho = H->rho; G.P = H->P; G.m = H->m;
+    G.vs = vs; G.us = us; G.idx = H->idx; G.cand = H->cand;
+    G.gx = H->gx; G.gv = H->gv; G.gu = H->gu; G.ga = H->ga; G.gdu = H->gdu; G.gh = H->gh; G.grho = H->grho;
+    G.gP = H->gP; G.gm = H->gm; G.gkey = H->gkey; G.gorder = H->gorder;
+    G.ctl = H->d_ctl; G.pad = H->pad; G.na = H->na; G.cand_cap = H->cand_cap; G.limit = H->cfg.limit;
+    G.from_alive = from_alive; G.nstaged = nstaged;
+    k_ghost_build<<<1, 1024, 0, H->stream>>>(G);
+    H->launches++;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
+int launch_density(sphb_handle *H, int root_alive, int root_ghosts, int check_old, double *Pn,
+                   bool want_omega = false) {
+    DensityArgs A;
+    A.x = H->x; A.m = H->m; A.h = H->h; A.rho = H->rho; A.P = H->P;
+    A.hn = H->hn; A.rhon = H->rhon; A.Pn = Pn;
+    A.omn = want_omega ? H->omn : nullptr; A.oms = want_omega ? H->oms : nullptr;
+    A.rec = H->rec; A.gsum = H->gsum;
+    A.cnt = H->cnt; A.ctl = H->d_ctl; A.pad = H->pad; A.na = H->na;
+    A.limit = H->cfg.limit; A.hfac = H->cfg.h_factor; A.m0 = H->m0;
+    A.root_ghosts = root_ghosts; A.root_alive = root_alive; A.check_old = check_old;
+    const int grid = nblk(H->na + 2 * H->pad, kTile);
+    const bool varh = H->opt.variable_h != 0;
+    if (varh && H->uniform_mass) k_density<true, true><<<grid, kTile, 0, H->stream>>>(A);
+    else if (varh) k_density<true, false><<<grid, kTile, 0, H->stream>>>(A);
+    else if (H->uniform_mass) k_density<false, true><<<grid, kTile, 0, H->stream>>>(A);
+    else k_density<false, false><<<grid, kTile, 0, H->stream>>>(A);
+    H->launches++;
+    CK(cudaGetLastError());
+    H->launches++;
+    if (root_alive || root_ghosts) H->have_counts = true;
+    return SPHB_OK;
+}
+
+template <int SEL>
+int launch_first_sel(sphb_handle *H, const SweepArgs &A) {
+    const int grid = nblk(H->na, kTile);
+    const bool adia = H->cfg.pressure_calc == SPHB_ADIABATIC;
+    if (adia && H->uniform_mass) k_force_first<SEL, true, true><<<grid, kTile, 0, H->stream>>>(A);
+    else if (adia) k_force_first<SEL, true, false><<<grid, kTile, 0, H->stream>>>(A);
+    else if (H->uniform_mass) k_force_first<SEL, false, true><<<grid, kTile, 0, H->stream>>>(A);
+    else k_force_first<SEL, false, false><<<grid, kTile, 0, H->stream>>>(A);
+    H->launches++;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
+int launch_refine(sphb_handle *H, SweepArgs A) {
+    const bool adia = H->cfg.pressure_calc == SPHB_ADIABATIC;
+    void *fn;
+    if (adia && H->uniform_mass) fn = (void *)k_force_refine<true, true>;
+    else if (adia) fn = (void *)k_force_refine<true, false>;
+    else if (H->uniform_mass) fn = (void *)k_force_refine<false, true>;
+    else fn = (void *)k_force_refine<false, false>;
+    int occ = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kTile, 0));
+    if (occ < 1) { H->err = "refinement kernel cannot be made resident"; return SPHB_ERR_CUDA; }
+    const int ntiles = nblk(H->na, kTile);
+    // a grid-wide barrier costs more the more CTAs take part: the few tiles around a front get one CTA
+    // per SM; a step whose predecessor queued many tiles gets every CTA that can be resident
+    const int want = H->refine_peak > 2 * H->num_sms ? occ * H->num_sms : H->num_sms;
+    int grid = std::min(ntiles, want);
+    if (grid < 1) grid = 1;
+    int max_sweeps = H->opt.max_sweeps;
+    void *args[] = {(void *)&A, (void *)&max_sweeps};
+    CK(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kTile), args, 0, H->stream));
+    H->launches++;
+    return SPHB_OK;
+}
+
+SweepArgs sweep_args(sphb_handle *H) {
+    SweepArgs A;
+    A.F.x = H->x; A.F.idx = H->idx; A.F.m = H->m;
+    A.F.rec = H->rec; A.F.gsum = H->gsum;
+    A.a = H->a; A.du = H->du; A.dirty = H->dirty; A.wl[0] = H->wl0; A.wl[1] = H->wl1; A.wl[2] = H->wl2; A.ctl = H->d_ctl;
+    A.pad = H->pad; A.na = H->na; A.m0 = H->m0; A.half_dt = H->cfg.t_i / 2;
+    A.epoch = H->epoch; A.kick = 1;
+    A.vn = H->vn; A.un = H->un;
+    return A;
+}
+
+// SPHSimulation::step_forward (sph_simulation.cpp:55-108) in phases; between them an x-slab run
+// exchanges halos with its neighbours (sphb_slab_*), a single-GPU run just goes on.
+//
+// The x-order check is optimistic: the kick-drift kernel raises a flag when two neighbours swapped
+// places, everything after it runs regardless and writes only into the next-state buffers, and
+// the flag is looked at together with the error word at the ONE host synchronisation at the end
+// of the step.  In the rare step where it is set, the alive block is radix-sorted and the phases
+// after the drift run again; nothing of the previous state has been overwritten by then.
+int step_begin(sphb_handle *H) {   // kick-drift + order flag, wall ghosts
+    if (H->epoch > 0x7fff0000 - 4 * H->opt.max_sweeps) {   // stamp wrap-around
+        CK(cudaMemsetAsync(H->dirty, 0, sizeof(int) * (size_t)nblk(H->cap_alive, kTile), H->stream));
+        H->epoch = 8;
+    }
+    phase_begin(H);
+    TRY(launch_begin(H, 1));
+    TRY(launch_kick(H, 1));
+    phase_end(H, 0);
+    if (H->opt.sort_every_step) {
+        TRY(sort_alive(H, false));
+        TRY(launch_begin(H, 1));
+        TRY(launch_kick(H, 0));   // ghost candidates refer to sorted slots: select again
+        phase_end(H, 1);
+    }
+    TRY(launch_ghost_build(H, 1, 0, H->vh, H->uh, H->vh, H->uh, true));
+    H->ghost_in_half = true;
+    phase_end(H, 2);
+    return SPHB_OK;
+}
+
+// after an attempt found the order flag set: sort, re-select the ghost candidates, rebuild the ghosts
+int step_resort(sphb_handle *H) {
+    CK(cudaMemcpyAsync(&H->d_ctl->fallbacks, &H->fallbacks_committed, sizeof(unsigned long long),
+                       cudaMemcpyHostToDevice, H->stream));
+    TRY(sort_alive(H, false));
+    TRY(launch_begin(H, 1));
+    TRY(launch_kick(H, 0));
+    TRY(launch_ghost_build(H, 1, 0, H->vh, H->uh, H->vh, H->uh, true));
+    H->epoch += H->opt.max_sweeps + 2;    // fresh stamps for the second attempt
+    return SPHB_OK;
+}
+
+int step_density(sphb_handle *H) {
+    TRY(launch_density(H, 1, 0, 1, H->Pn));
+    phase_end(H, 3);
+    return SPHB_OK;
+}
+
+SweepArgs step_sweep_args(sphb_handle *H) {
+    SweepArgs A = sweep_args(H);
+    A.a = H->an; A.du = H->dun;       // the previous a, du stay intact until step_finish
+    A.Pstale = H->P; A.Pout = H->Pn;
+    A.vh = H->vh; A.uh = H->uh;
+    A.F.vA = H->vh; A.F.uA = H->uh;
+    A.F.vB = H->vh; A.F.uB = H->uh;
+    return A;
+}
+
+int step_force_first(sphb_handle *H) {
+    SweepArgs A = step_sweep_args(H);
+    if (H->opt.order == SPHB_ORDER_JACOBI) TRY(launch_first_sel<SEL_ALIVE>(H, A));
+    else TRY(launch_first_sel<SEL_INDEX>(H, A));
+    phase_end(H, 4);
+    return SPHB_OK;
+}
+
+int step_refine(sphb_handle *H) {   // runs until this handle's work list is empty
+    if (H->opt.order == SPHB_ORDER_JACOBI) return SPHB_OK;
+    SweepArgs A = step_sweep_args(H);
+    A.F.vA = H->vn; A.F.uA = H->un;   // lower-index neighbours are seen fully kicked
+    TRY(launch_refine(H, A));
+    phase_end(H, 5);
+    return SPHB_OK;
+}
+
+// device flags of the attempt in flight: one small D2H copy + stream synchronisation
+int step_flags(sphb_handle *H, int *err, int *unsorted, int *halo_changed) {
+    CK(cudaMemcpyAsync(H->h_ctl, H->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaStreamSynchronize(H->stream));
+    *err = H->h_ctl->err_code;
+    *unsorted = H->h_ctl->unsorted;
+    *halo_changed = H->h_ctl->halo_changed;
+    return SPHB_OK;
+}
+
+int step_error(sphb_handle *H) {    // turn the error word just read into a status
+    char b[256];
+    snprintf(b, sizeof b, "%s (sorted slot %d)", err_text(H->h_ctl->err_code), H->h_ctl->err_particle);
+    H->err = b;
+    const int code = H->h_ctl->err_code;
+    CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, 2 * sizeof(int), H->stream));
+    return code;
+}
+
+int step_finish(sphb_handle *H) {
+    H->epoch += H->opt.max_sweeps + 2;
+    std::swap(H->v, H->vn);
+    std::swap(H->u, H->un);
+    std::swap(H->h, H->hn);
+    std::swap(H->rho, H->rhon);
+    std::swap(H->P, H->Pn);
+    std::swap(H->a, H->an);
+    std::swap(H->du, H->dun);
+    H->steps++;
+    H->fallbacks_committed = H->h_ctl->fallbacks;
+    H->refine_peak = H->h_ctl->nwork_peak;
+    const int used = (H->opt.order == SPHB_ORDER_JACOBI) ? 1 : H->h_ctl->sweeps_used;
+    H->sweeps_last = used;
+    H->sweeps_total += used;
+    H->cfg.n_ghost = wall_ghosts(H);
+    H->cfg.n_part = H->na + H->cfg.n_ghost;
+    phase_collect(H);
+    return SPHB_OK;
+}
+
+int step_once(sphb_handle *H) {
+    TRY(step_begin(H));
+    for (int attempt = 0;; attempt++) {
+        TRY(step_density(H));
+        TRY(step_force_first(H));
+        TRY(step_refine(H));
+        int err, unsorted, changed;
+        TRY(step_flags(H, &err, &unsorted, &changed));
+        if (unsorted && attempt == 0) {
+            // whatever the kernels complained about came from the broken order: forget it, sort, redo
+            CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, 2 * sizeof(int), H->stream));
+            TRY(step_resort(H));
+            continue;
+        }
+        if (unsorted) { H->err = err_text(SPHB_ERR_UNSORTED); return SPHB_ERR_UNSORTED; }
+        if (err) return step_error(H);
+        break;
+    }
+    return step_finish(H);
+}
+
+int ensure_aos(sphb_handle *H, size_t n) {
+    if (H->aos_cap >= n) return SPHB_OK;
+    if (H->d_aos) CK(cudaFree(H->d_aos));
+    H->d_aos = nullptr;
+    size_t want = (size_t)H->cap_alive + 2 * (size_t)H->pad;
+    if (want < n) want = n;
+    CK(cudaMalloc((void **)&H->d_aos, sizeof(AosRec) * want));
+    H->aos_cap = want;
+    return SPHB_OK;
+}
+
+PackArgs pack_args(sphb_handle *H) {
+    PackArgs A;
+    A.x = H->x; A.v = H->v; A.u = H->u; A.a = H->a; A.du = H->du; A.h = H->h; A.rho = H->rho; A.P = H->P; A.m = H->m;
+    A.idx = H->idx; A.slot_id = H->slot_id;
+    A.gx = H->gx; A.gv = H->gv; A.gu = H->gu; A.ga = H->ga; A.gdu = H->gdu; A.gh = H->gh; A.grho = H->grho;
+    A.gP = H->gP; A.gm = H->gm; A.gkey = H->gkey;
+    A.vg = H->ghost_in_half ? H->vh : H->v;
+    A.ug = H->ghost_in_half ? H->uh : H->u;
+    A.gorder = H->gorder; A.cnt = H->cnt; A.aos = H->d_aos;
+    A.out_newton = nullptr; A.out_nbr = nullptr;
+    A.ctl = H->d_ctl; A.pad = H->pad; A.na = H->na; A.ng = 0;
+    A.idx_base = (unsigned)H->idx_base;
+    return A;
+}
+
+// make sure the ghosts' v,u are in the pads of the CURRENT v,u arrays
+int ghosts_to_current(sphb_handle *H) {
+    if (!H->ghost_in_half) return SPHB_OK;
+    k_copy_pads<<<4, 256, 0, H->stream>>>(H->vh, H->uh, H->v, H->u, H->d_ctl, H->pad, H->na);
+    H->launches++;
+    CK(cudaGetLastError());
+    H->ghost_in_half = false;
+    return SPHB_OK;
+}
+
+int pack_to_staging(sphb_handle *H, bool with_counts, int *n_total) {
+    TRY(read_ctl(H));
+    const int ng = wall_ghosts(H);
+    const int n = H->na + ng;
+    TRY(ensure_aos(H, (size_t)n));
+    PackArgs A = pack_args(H);
+    A.ng = ng;
+    if (with_counts) {
+        if (!H->d_newton) {
+            TRY(dalloc(H, &H->d_newton, (size_t)H->cap_alive + 2 * H->pad));
+            TRY(dalloc(H, &H->d_nbr, (size_t)H->cap_alive + 2 * H->pad));
+        }
+        A.out_newton = H->d_newton; A.out_nbr = H->d_nbr;
+    }
+    if (n > 0) {
+        k_pack<<<nblk(n, 256), 256, 0, H->stream>>>(A);
+        H->launches++;
+        CK(cudaGetLastError());
+    }
+    *n_total = n;
+    return SPHB_OK;
+}
+
+}  // namespace
+
+namespace {
+SlabArgs slab_args(sphb_handle *H, int side) {
+    SlabArgs A;
+    A.x = H->x; A.m = H->m; A.vh = H->vh; A.uh = H->uh; A.vn = H->vn; A.un = H->un;
+    A.h = H->h; A.rho = H->rho; A.P = H->P; A.idx = H->idx; A.rec = H->rec;
+    A.dirty = H->dirty; A.wl[0] = H->wl0; A.wl[1] = H->wl1; A.wl[2] = H->wl2; A.ctl = H->d_ctl;
+    A.pad = H->pad; A.na = H->na; A.K = H->K; A.side = side;
+    return A;
+}
+int slab_flags(sphb_handle *H) {
+    k_slab_flags<<<1, 1, 0, H->stream>>>(H->d_ctl, H->halo_l ? 1 : 0, H->halo_r ? 1 : 0);
+    H->launches++;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+}  // namespace
+
+namespace {
+struct NcclApi {
+    void *lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    std::string err;
+    bool load() {
+        if (lib) return true;
+        for (const char *name : {"libnccl.so.2", "libnccl.so"}) {
+            lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+            if (lib) break;
+        }
+        if (!lib) { err = std::string("cannot open libnccl: ") + dlerror(); return false; }
+#define SPHB_SYM(F) F = reinterpret_cast<decltype(F)>(dlsym(lib, "nccl" #F)); if (!F) { err = "libnccl lacks nccl" #F; lib = nullptr; return false; }
+        SPHB_SYM(GetUniqueId) SPHB_SYM(CommInitRank) SPHB_SYM(CommDestroy) SPHB_SYM(Send) SPHB_SYM(Recv)
+        SPHB_SYM(AllReduce) SPHB_SYM(GroupStart) SPHB_SYM(GroupEnd) SPHB_SYM(GetErrorString)
+#undef SPHB_SYM
+        return true;
+    }
+};
+NcclApi g_nccl;
+
+#define NK(call)                                                                          \
+    do {                                                                                  \
+        ncclResult_t r_ = (call);                                                         \
+        if (r_ != ncclSuccess) {                                                          \
+            H->err = std::string(#call) + ": " + g_nccl.GetErrorString(r_);               \
+            return SPHB_ERR_CUDA;                                                         \
+        }                                                                                 \
+    } while (0)
+
+__global__ void k_flags(const Ctl *ctl, int *flags) {
+    flags[0] = ctl->err_code;
+    flags[1] = ctl->unsorted;
+    flags[2] = ctl->halo_changed;
+}
+
+// pack both edges, one grouped send/recv with the neighbours, unpack both pads
+int native_exchange(sphb_handle *H, int what) {
+    const int n = sphb_slab_message_doubles(H, what);
+    for (int k = 0; k < 2; k++) {
+        const int side = k ? 1 : -1;
+        if (k ? H->halo_r : H->halo_l) TRY(sphb_slab_pack(H, what, side, H->msg_send[what][k]));
+    }
+    NK(g_nccl.GroupStart());
+    for (int k = 0; k < 2; k++) {
+        if (!(k ? H->halo_r : H->halo_l)) continue;
+        const int peer = H->rank + (k ? 1 : -1);
+        NK(g_nccl.Send(H->msg_send[what][k], (size_t)n, ncclFloat64, peer, H->comm, H->stream));
+        NK(g_nccl.Recv(H->msg_recv[what][k], (size_t)n, ncclFloat64, peer, H->comm, H->stream));
+    }
+    NK(g_nccl.GroupEnd());
+    for (int k = 0; k < 2; k++) {
+        const int side = k ? 1 : -1;
+        if (k ? H->halo_r : H->halo_l) TRY(sphb_slab_unpack(H, what, side, H->msg_recv[what][k]));
+    }
+    return SPHB_OK;
+}
+
+// everything of a step after the drift, up to the agreed flags (the step's one host synchronisation)
+int native_attempt(sphb_handle *H, int *rounds) {
+    TRY(native_exchange(H, MSG_BASE));
+    TRY(step_density(H));
+    TRY(native_exchange(H, MSG_RECORDS));
+    TRY(step_force_first(H));
+    TRY(step_refine(H));
+    for (int r = 0; r < H->fixed_rounds; r++) {
+        TRY(native_exchange(H, MSG_ITERATE));
+        TRY(step_refine(H));
+    }
+    TRY(native_exchange(H, MSG_ITERATE));     // check only: its unpack raises halo_changed if anything still moved
+    *rounds = H->fixed_rounds + 1;
+    return SPHB_OK;
+}
+
+int native_flags(sphb_handle *H) {   // -> H->h_flags[0..2] = MAX over ranks; H->h_ctl = my control block
+    k_flags<<<1, 1, 0, H->stream>>>(H->d_ctl, H->d_flags);
+    H->launches++;
+    CK(cudaGetLastError());
+    NK(g_nccl.AllReduce(H->d_flags, H->d_flags, 3, ncclInt32, ncclMax, H->comm, H->stream));
+    CK(cudaMemcpyAsync(H->h_flags, H->d_flags, 3 * sizeof(int), cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaMemcpyAsync(H->h_ctl, H->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaStreamSynchronize(H->stream));
+    return SPHB_OK;
+}
+}  // namespace
+
+extern "C" {
+
+const char *sphb_build_arch(void) { return "sm_100a"; }
+
+void sphb_default_options(sphb_options *opt) {
+    memset(opt, 0, sizeof *opt);
+    opt->variable_h = 1;
+    opt->fixed_h = 0.2;   // CONSTANT_H, define.hpp:29
+    opt->order = SPHB_ORDER_REFERENCE;
+    opt->max_sweeps = 64;
+    opt->device = -1;
+    opt->pad_capacity = 4096;
+    opt->capacity = 0;
+    opt->sort_every_step = 0;
+}
+
+static sphb_handle g_null_handle_for_errors;
+
+const char *sphb_last_error(const sphb_handle *h) {
+    return h ? h->err.c_str() : g_null_handle_for_errors.err.c_str();
+}
+
+int sphb_create(const sphb_config *cfg, const sphb_options *opt_in, sphb_handle **out) {
+    sphb_handle *H = &g_null_handle_for_errors;
+    if (!cfg || !out) { H->err = "null argument"; return SPHB_ERR_INVALID; }
+    *out = nullptr;
+    sphb_options opt;
+    if (opt_in) opt = *opt_in; else sphb_default_options(&opt);
+    if (cfg->n_part < 1 || cfg->n_ghost < 0 || cfg->n_ghost > cfg->n_part) { H->err = "bad n_part / n_ghost"; return SPHB_ERR_INVALID; }
+    if (opt.pad_capacity < 1 || opt.max_sweeps < 1) { H->err = "bad options"; return SPHB_ERR_INVALID; }
+    if (cfg->pressure_calc != SPHB_ISOTHERMAL && cfg->pressure_calc != SPHB_ADIABATIC) {
+        H->err = "Unknown pressure calculation mode!";   // calculators.cpp:80-82
+        return SPHB_ERR_INVALID;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        H->err = "no CUDA device: libsphb has no CPU fallback";
+        return SPHB_ERR_NO_DEVICE;
+    }
+    H = new sphb_handle();
+    H->cfg = *cfg;
+    H->opt = opt;
+    int dev = opt.device;
+    if (dev < 0) { if (cudaGetDevice(&dev) != cudaSuccess) dev = 0; }
+    H->device = dev;
+    auto fail = [&](int rc) { g_null_handle_for_errors.err = H->err; sphb_destroy(H); return rc; };
+#define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { H->err = std::string(#call) + ": " + cudaGetErrorString(e_); return fail(SPHB_ERR_CUDA); } } while (0)
+    CKC(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    CKC(cudaGetDeviceProperties(&prop, dev));
+    H->num_sms = prop.multiProcessorCount;
+    if (prop.major < 10) {
+        H->err = "libsphb is built for sm_100a only (found sm_" + std::to_string(prop.major) + std::to_string(prop.minor) + ")";
+        return fail(SPHB_ERR_NO_DEVICE);
+    }
+    CKC(cudaStreamCreateWithFlags(&H->own_stream, cudaStreamNonBlocking));
+    H->stream = H->own_stream;
+    const int n_alive = cfg->n_part - cfg->n_ghost;
+    H->cap_alive = std::max(opt.capacity, n_alive);
+    H->pad = opt.pad_capacity;
+    H->cand_cap = 2 * H->pad;
+    H->total = H->cap_alive + 2 * H->pad;
+    H->na = n_alive;
+    H->m0 = cfg->mass;
+    const size_t T = (size_t)H->total;
+    double **darr[] = {&H->x, &H->v, &H->u, &H->a, &H->du, &H->h, &H->rho, &H->P, &H->m, &H->xalt, &H->vh,
+                       &H->uh, &H->vn, &H->un, &H->hn, &H->rhon, &H->omn, &H->oms, &H->Pn, &H->tmp, &H->an, &H->dun};
+    for (double **p : darr) { int rc = dalloc(H, p, T); if (rc) return fail(rc); }
+    double **garr[] = {&H->gx, &H->gv, &H->gu, &H->ga, &H->gdu, &H->gh, &H->grho, &H->gP, &H->gm};
+    for (double **p : garr) { int rc = dalloc(H, p, (size_t)H->cand_cap); if (rc) return fail(rc); }
+    int rc = 0;
+    rc |= dalloc(H, &H->idx, T); rc |= dalloc(H, &H->idx_alt, T); rc |= dalloc(H, &H->slot_id, T);
+    rc |= dalloc(H, &H->cnt, T); rc |= dalloc(H, &H->dirty, (size_t)nblk(H->cap_alive, kTile) + 1);
+    rc |= dalloc(H, &H->cand, (size_t)H->cand_cap); rc |= dalloc(H, &H->gorder, (size_t)H->cand_cap);
+    rc |= dalloc(H, &H->perm, (size_t)H->cap_alive); rc |= dalloc(H, &H->iota, (size_t)H->cap_alive);
+    rc |= dalloc(H, &H->gkey, (size_t)H->cand_cap); rc |= dalloc(H, &H->d_ctl, 1);
+    rc |= dalloc(H, &H->wl0, (size_t)nblk(H->cap_alive, kTile) + 1); rc |= dalloc(H, &H->wl1, (size_t)nblk(H->cap_alive, kTile) + 1);
+    rc |= dalloc(H, &H->wl2, (size_t)nblk(H->cap_alive, kTile) + 1);
+    rc |= dalloc(H, &H->rec, T); rc |= dalloc(H, &H->gsum, T);
+    if (rc) return fail(SPHB_ERR_CUDA);
+    CKC(cudaMallocHost((void **)&H->h_ctl, sizeof(Ctl)));
+    memset(H->h_ctl, 0, sizeof(Ctl));
+    size_t bytes = 0;
+    CKC(cub::DeviceRadixSort::SortPairs(nullptr, bytes, (double *)nullptr, (double *)nullptr, (int *)nullptr,
+                                        (int *)nullptr, H->cap_alive, 0, 64, H->stream));
+    H->cub_bytes = bytes;
+    CKC(cudaMalloc(&H->cub_tmp, std::max<size_t>(bytes, 16)));
+    for (int i = 0; i <= SPHB_PHASES; i++) CKC(cudaEventCreate(&H->ev[i]));
+    CKC(cudaStreamSynchronize(H->stream));
+#undef CKC
+    *out = H;
+    return SPHB_OK;
+}
+
+void sphb_destroy(sphb_handle *H) {
+    if (!H || H == &g_null_handle_for_errors) return;
+    cudaSetDevice(H->device);
+    if (H->stream) cudaStreamSynchronize(H->stream);
+    void *ptrs[] = {H->an, H->dun, H->x, H->v, H->u, H->a, H->du, H->h, H->rho, H->P, H->m, H->xalt, H->vh, H->uh, H->vn, H->un,
+                    H->hn, H->rhon, H->omn, H->oms, H->Pn, H->tmp, H->gx, H->gv, H->gu, H->ga, H->gdu, H->gh,
+                    H->grho, H->gP, H->gm, H->idx, H->idx_alt, H->slot_id, H->cnt, H->dirty, H->cand, H->gorder,
+                    H->perm, H->iota, H->gkey, H->d_ctl, H->cub_tmp, H->d_aos, H->d_newton, H->d_nbr,
+                    H->wl0, H->wl1, H->wl2, H->rec, H->gsum};
+    for (void *p : ptrs) if (p) cudaFree(p);
+    if (H->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(H->comm);
+    for (int w = 0; w < 3; w++) for (int k = 0; k < 2; k++) { if (H->msg_send[w][k]) cudaFree(H->msg_send[w][k]); if (H->msg_recv[w][k]) cudaFree(H->msg_recv[w][k]); }
+    if (H->d_flags) cudaFree(H->d_flags);
+    if (H->h_flags) cudaFreeHost(H->h_flags);
+    if (H->h_ctl) cudaFreeHost(H->h_ctl);
+    for (int i = 0; i <= SPHB_PHASES; i++) if (H->ev[i]) cudaEventDestroy(H->ev[i]);
+    if (H->own_stream) cudaStreamDestroy(H->own_stream);
+    delete H;
+}
+
+int sphb_set_stream(sphb_handle *H, void *cuda_stream) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    CK(cudaStreamSynchronize(H->stream));
+    H->stream = cuda_stream ? (cudaStream_t)cuda_stream : H->own_stream;
+    return SPHB_OK;
+}
+
+int sphb_get_config(const sphb_handle *H, sphb_config *out) {
+    if (!H || !out) return SPHB_ERR_INVALID;
+    *out = H->cfg;
+    return SPHB_OK;
+}
+
+int sphb_upload(sphb_handle *H, const sphb_particle *aos, int n_part, int n_ghost) {
+    if (!H) return SPHB_ERR_INVALID;
+    if (!aos || n_part < 1 || n_ghost < 0 || n_ghost > n_part) { H->err = "bad upload arguments"; return SPHB_ERR_INVALID; }
+    const int na = n_part - n_ghost;
+    if (na > H->cap_alive || n_ghost > H->cand_cap) { H->err = "upload exceeds the handle's capacity"; return SPHB_ERR_CAPACITY; }
+    CK(cudaSetDevice(H->device));
+    TRY(ensure_aos(H, (size_t)n_part));
+    CK(cudaMemcpyAsync(H->d_aos, aos, sizeof(AosRec) * (size_t)n_part, cudaMemcpyHostToDevice, H->stream));
+    // uniform masses let every kernel take m from a register instead of a per-neighbour load
+    bool uniform = true;
+    const double m0 = aos[0].mass;
+    for (int i = 1; i < n_part && uniform; i++) uniform = (aos[i].mass == m0);
+    H->uniform_mass = uniform;
+    H->m0 = m0;
+    H->na = na;
+    H->cfg.n_part = n_part;
+    H->cfg.n_ghost = n_ghost;
+    PackArgs A = pack_args(H);
+    A.ng = n_ghost;
+    k_unpack<<<nblk(n_part, 256), 256, 0, H->stream>>>(A);
+    H->launches++;
+    CK(cudaGetLastError());
+    TRY(launch_begin(H, 1));
+    k_check_sorted<<<nblk(na, kTile), kTile, 0, H->stream>>>(H->x, H->d_ctl, H->pad, na);
+    H->launches++;
+    CK(cudaGetLastError());
+    TRY(read_ctl(H));
+    if (H->h_ctl->unsorted) TRY(sort_alive(H, true));
+    TRY(launch_ghost_build(H, 0, n_ghost, H->v, H->u, H->v, H->u));
+    H->ghost_in_half = false;
+    H->have_counts = false;
+    return read_ctl(H);
+}
+
+int sphb_download(sphb_handle *H, sphb_particle *aos, int cap, int *n_part, int *n_ghost, int write_ids) {
+    if (!H || !aos) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    int n = 0;
+    TRY(pack_to_staging(H, false, &n));
+    if (n > cap) { H->err = "download buffer too small"; return SPHB_ERR_CAPACITY; }
+    if (write_ids) {
+        CK(cudaMemcpyAsync(aos, H->d_aos, sizeof(AosRec) * (size_t)n, cudaMemcpyDeviceToHost, H->stream));
+    } else {
+        // leave the 8 leading bytes (const int id + padding) of every record alone
+        CK(cudaMemcpy2DAsync((char *)aos + 8, sizeof(AosRec), (const char *)H->d_aos + 8, sizeof(AosRec), 80,
+                             (size_t)n, cudaMemcpyDeviceToHost, H->stream));
+    }
+    CK(cudaStreamSynchronize(H->stream));
+    const int ng = n - H->na;
+    H->cfg.n_part = n;
+    H->cfg.n_ghost = ng;
+    if (n_part) *n_part = n;
+    if (n_ghost) *n_ghost = ng;
+    return SPHB_OK;
+}
+
+int sphb_download_fields(sphb_handle *H, double *fields, int *type, int cap, int *n_part, int *n_ghost) {
+    if (!H || !fields) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    int n = 0;
+    TRY(pack_to_staging(H, false, &n));
+    if (n > cap) { H->err = "download buffer too small"; return SPHB_ERR_CAPACITY; }
+    std::vector<AosRec> tmp((size_t)n);
+    CK(cudaMemcpyAsync(tmp.data(), H->d_aos, sizeof(AosRec) * (size_t)n, cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaStreamSynchronize(H->stream));
+    for (int i = 0; i < n; i++) {
+        const AosRec &r = tmp[(size_t)i];
+        double *f = fields + 9 * (size_t)i;
+        f[0] = r.mass; f[1] = r.pos; f[2] = r.vel; f[3] = r.acc; f[4] = r.h;
+        f[5] = r.du_dt; f[6] = r.u; f[7] = r.density; f[8] = r.pressure;
+        if (type) type[i] = r.type;
+    }
+    if (n_part) *n_part = n;
+    if (n_ghost) *n_ghost = n - H->na;
+    return SPHB_OK;
+}
+
+int sphb_download_counts(sphb_handle *H, int *newton_iters, int *neighbours, int cap) {
+    if (!H || !newton_iters || !neighbours) return SPHB_ERR_INVALID;
+    if (!H->have_counts) { H->err = "no density pass has run yet"; return SPHB_ERR_INVALID; }
+    CK(cudaSetDevice(H->device));
+    int n = 0;
+    TRY(pack_to_staging(H, true, &n));
+    if (n > cap) { H->err = "download buffer too small"; return SPHB_ERR_CAPACITY; }
+    CK(cudaMemcpyAsync(newton_iters, H->d_newton, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaMemcpyAsync(neighbours, H->d_nbr, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaStreamSynchronize(H->stream));
+    return SPHB_OK;
+}
+
+int sphb_kick_drift(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    TRY(launch_begin(H, 1));
+    TRY(launch_kick(H, 1));
+    // function-level semantics: the kicked values become the particle's v, u
+    std::swap(H->v, H->vh);
+    std::swap(H->u, H->uh);
+    TRY(read_ctl(H));
+    if (H->h_ctl->unsorted) TRY(sort_alive(H, true));
+    H->ghost_in_half = false;
+    return SPHB_OK;
+}
+
+int sphb_ghosts(sphb_handle *H, int *n_ghost) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    TRY(launch_begin(H, 1));
+    TRY(launch_kick(H, 0));
+    TRY(read_ctl(H));
+    if (H->h_ctl->unsorted) { H->err = err_text(SPHB_ERR_UNSORTED); return SPHB_ERR_UNSORTED; }
+    TRY(launch_ghost_build(H, 1, 0, H->v, H->u, H->v, H->u));
+    H->ghost_in_half = false;
+    TRY(read_ctl(H));
+    const int ng = wall_ghosts(H);
+    H->cfg.n_ghost = ng;
+    H->cfg.n_part = H->na + ng;
+    if (n_ghost) *n_ghost = ng;
+    return SPHB_OK;
+}
+
+int sphb_density(sphb_handle *H, int include_ghosts) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    TRY(ghosts_to_current(H));
+    TRY(launch_begin(H, 0));
+    TRY(launch_density(H, 1, include_ghosts ? 1 : 0, 0, H->P));
+    // in place, like dc(p): the particle's h and density are replaced
+    std::swap(H->h, H->hn);
+    std::swap(H->rho, H->rhon);
+    return read_ctl(H);
+}
+
+// records (omega, 1/h^5, ...) of every particle for its stored h, density — first half of sphb_forces
+int sphb_slab_records(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    TRY(ghosts_to_current(H));
+    TRY(launch_begin(H, 0));
+    // omega of every particle for its stored h, density (calc_omega), nothing else changes
+    return launch_density(H, 0, 0, 0, H->P);
+}
+// second half of sphb_forces: the order-independent acceleration / du_dt pass, no kick
+int sphb_slab_forces(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    SweepArgs A = sweep_args(H);
+    A.kick = 0;
+    A.Pstale = H->P; A.Pout = H->P;
+    A.vh = H->v; A.uh = H->u;
+    A.F.vA = H->v; A.F.uA = H->u;
+    A.F.vB = H->v; A.F.uB = H->u;
+    TRY(launch_first_sel<SEL_ALL_A>(H, A));
+    return read_ctl(H);
+}
+
+int sphb_forces(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    TRY(sphb_slab_records(H));
+    return sphb_slab_forces(H);
+}
+
+int sphb_omega(sphb_handle *H, double *omega, int cap) {
+    if (!H || !omega) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    TRY(ghosts_to_current(H));
+    TRY(launch_begin(H, 0));
+    TRY(launch_density(H, 0, 0, 0, H->P, true));   // omega only: h, density stay as stored
+    TRY(read_ctl(H));
+    const int n = H->na + wall_ghosts(H);
+    if (n > cap) { H->err = "download buffer too small"; return SPHB_ERR_CAPACITY; }
+    k_pack_f64<<<nblk(n, 256), 256, 0, H->stream>>>(H->omn, H->tmp, H->idx, H->gorder, H->d_ctl, H->pad, H->na,
+                                                    n - H->na, (unsigned)H->idx_base);
+    H->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(omega, H->tmp, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaStreamSynchronize(H->stream));
+    return SPHB_OK;
+}
+
+int sphb_step(sphb_handle *H, int nsteps) {
+    if (!H || nsteps < 0) return SPHB_ERR_INVALID;
+    if (H->slab) { H->err = "x-slab runs step phase by phase (sphb_slab_*), with halo exchanges in between"; return SPHB_ERR_INVALID; }
+    CK(cudaSetDevice(H->device));
+    for (int k = 0; k < nsteps; k++) TRY(step_once(H));   // one host synchronisation per step (its flags)
+    return SPHB_OK;
+}
+
+// lattice of setup.cpp:145-185 for this handle's particles (all of them, or global indices
+// [idx_base, idx_base + na) of an x-slab run); no ghosts, no densities yet
+int sphb_slab_init_lattice(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    const long long n = H->slab ? H->n_global : (long long)H->na;
+    if (n < 2) { H->err = "need at least 2 particles"; return SPHB_ERR_INVALID; }
+    // setup.cpp:145-153,158-159, same operations in the same order
+    double max_x = H->cfg.limit;
+    double min_x = -max_x;
+    double spacing = (max_x - min_x) / (n - 1);
+    max_x -= spacing / 2;
+    min_x += spacing / 2;
+    const double spacing2 = (max_x - min_x) / (n - 1);
+    LatticeArgs L;
+    L.x = H->x; L.v = H->v; L.u = H->u; L.a = H->a; L.du = H->du; L.h = H->h; L.rho = H->rho; L.P = H->P; L.m = H->m;
+    L.idx = H->idx; L.slot_id = H->slot_id; L.pad = H->pad; L.na = H->na; L.i0 = H->slab ? H->idx_base : 0;
+    L.min_x = min_x; L.spacing = spacing2; L.v0 = H->cfg.v_0;
+    L.u0 = (H->cfg.pressure_calc == SPHB_ADIABATIC) ? 1 / (kGamma - 1) : 0.0;
+    L.h0 = H->opt.variable_h ? H->cfg.h_factor * spacing2 : H->opt.fixed_h;
+    L.mass = H->cfg.mass;
+    H->uniform_mass = true;
+    H->m0 = H->cfg.mass;
+    k_lattice<<<nblk(H->na, 256), 256, 0, H->stream>>>(L);
+    H->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemsetAsync(H->d_ctl, 0, sizeof(Ctl), H->stream));   // no ghosts yet
+    H->ghost_in_half = false;
+    return slab_flags(H);
+}
+
+// v_i = +-c_s from the pre-pass density (setup.cpp:197-201)
+int sphb_slab_prepass(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    k_prepass<<<nblk(H->na, 256), 256, 0, H->stream>>>(H->x, H->v, H->u, H->rho, H->P, H->pad, H->na);
+    H->launches++;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
+int sphb_init_lattice(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    if (H->slab) { H->err = "x-slab runs initialise phase by phase (sphb_slab_*), with halo exchanges in between"; return SPHB_ERR_INVALID; }
+    TRY(sphb_slab_init_lattice(H));
+    if (H->cfg.pressure_calc == SPHB_ADIABATIC) {
+        // pre-pass, setup.cpp:192-202
+        TRY(sphb_density(H, 0));
+        TRY(sphb_slab_prepass(H));
+    }
+    TRY(sphb_ghosts(H, nullptr));
+    TRY(sphb_density(H, 1));
+    return sphb_forces(H);
+}
+
+// ------------------------------------------------------------------------------------
+// x-slab decomposition across the GPUs of a node.  The library does the
+// device work of every phase and packs / unpacks halo messages in caller-owned device
+// buffers; moving the messages between ranks (NCCL send/recv, or a device copy when the
+// ranks share a process) is the caller's part — sph_b200/slabs.py.
+
+int sphb_slab_configure(sphb_handle *H, int rank, int world, int halo_count, long long index_offset,
+                        long long n_global) {
+    if (!H) return SPHB_ERR_INVALID;
+    if (world < 1 || rank < 0 || rank >= world || halo_count < 1 || halo_count > H->pad || index_offset < 0 ||
+        n_global < H->na || index_offset + H->na > n_global || n_global >= (1ll << 31)) {
+        H->err = "bad slab configuration (halo_count must fit pad_capacity; global indices must fit 31 bits)";
+        return SPHB_ERR_INVALID;
+    }
+    CK(cudaSetDevice(H->device));
+    H->slab = world > 1;
+    H->rank = rank; H->world = world; H->K = halo_count;
+    H->idx_base = index_offset; H->n_global = n_global;
+    H->halo_l = rank > 0;
+    H->halo_r = rank < world - 1;
+    return slab_flags(H);
+}
+
+int sphb_slab_message_doubles(const sphb_handle *H, int what) {
+    if (!H || what < 0 || what > 2 || H->K < 1) return -1;
+    return msg_rows(what) * H->K + 8;
+}
+
+int sphb_slab_pack(sphb_handle *H, int what, int side, double *d_buf) {
+    if (!H || !d_buf || what < 0 || what > 2 || (side != -1 && side != 1)) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    SlabArgs A = slab_args(H, side);
+    if (what == MSG_BASE && !H->ghost_in_half) { A.vh = H->v; A.uh = H->u; }   // t = 0: the current v, u
+    k_slab_pack<<<std::max(1, std::min(nblk(H->K, 256), 64)), 256, 0, H->stream>>>(A, what, d_buf);
+    H->launches++;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
+int sphb_slab_unpack(sphb_handle *H, int what, int side, const double *d_buf) {
+    if (!H || !d_buf || what < 0 || what > 2 || (side != -1 && side != 1)) return SPHB_ERR_INVALID;
+    if ((side < 0 && !H->halo_l) || (side > 0 && !H->halo_r)) { H->err = "no neighbouring slab on that side"; return SPHB_ERR_INVALID; }
+    CK(cudaSetDevice(H->device));
+    SlabArgs A = slab_args(H, side);
+    if (what == MSG_BASE && !H->ghost_in_half) { A.vh = H->v; A.uh = H->u; }
+    k_slab_unpack<<<1, 1024, 0, H->stream>>>(A, what, d_buf);
+    H->launches++;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
+int sphb_slab_step_begin(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    return step_begin(H);
+}
+int sphb_slab_density(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    return step_density(H);
+}
+int sphb_slab_force_first(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    return step_force_first(H);
+}
+int sphb_slab_refine(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    return step_refine(H);
+}
+// The flags of the attempt in flight (the one host synchronisation of a slab step):
+//   flags[0] error code raised on the device (0 = none), flags[1] x-order broken by the drift,
+//   flags[2] the last ITERATE unpack differed from the copy held here (sweep not known finished).
+// Nothing is raised here: the ranks first agree (MAX over ranks) on what to do.
+int sphb_slab_poll(sphb_handle *H, int *flags) {
+    if (!H || !flags) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    return step_flags(H, &flags[0], &flags[1], &flags[2]);
+}
+// some rank's order flag was set: sort (if mine was), forget the attempt's errors, rebuild the ghosts
+int sphb_slab_resort(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, 2 * sizeof(int), H->stream));
+    if (H->h_ctl->unsorted) return step_resort(H);
+    TRY(launch_begin(H, 1));
+    TRY(launch_kick(H, 0));
+    TRY(launch_ghost_build(H, 1, 0, H->vh, H->uh, H->vh, H->uh, true));
+    H->epoch += H->opt.max_sweeps + 2;
+    return SPHB_OK;
+}
+// turn the error word seen by the last poll into this handle's status and message
+int sphb_slab_raise(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    if (H->h_ctl->err_code == 0) return SPHB_OK;
+    return step_error(H);
+}
+int sphb_slab_step_end(sphb_handle *H) {
+    if (!H) return SPHB_ERR_INVALID;
+    return step_finish(H);
+}
+
+// ------------------------------------------------------------------------------------
+// The same protocol driven from C++: one NCCL communicator per handle, halo messages sent
+// to the direct neighbours with grouped ncclSend/ncclRecv on the handle's stream, the three
+// step flags agreed with one small ncclAllReduce(MAX).  A step costs the host a dozen launches
+// and ONE stream synchronisation.  libnccl is opened at run time (dlopen), so libsphb.so itself
+// has no link-time dependency on it.
+
+int sphb_nccl_unique_id(void *out128) {
+    sphb_handle *H = &g_null_handle_for_errors;
+    if (!out128) return SPHB_ERR_INVALID;
+    if (!g_nccl.load()) { H->err = g_nccl.err; return SPHB_ERR_NO_DEVICE; }
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId");
+    NK(g_nccl.GetUniqueId(reinterpret_cast<ncclUniqueId *>(out128)));
+    return SPHB_OK;
+}
+
+int sphb_slab_comm_init(sphb_handle *H, const void *unique_id128) {
+    if (!H || !unique_id128) return SPHB_ERR_INVALID;
+    if (!H->slab) { H->err = "sphb_slab_configure with world > 1 comes first"; return SPHB_ERR_INVALID; }
+    if (!g_nccl.load()) { H->err = g_nccl.err; return SPHB_ERR_NO_DEVICE; }
+    CK(cudaSetDevice(H->device));
+    ncclUniqueId id;
+    memcpy(&id, unique_id128, sizeof id);
+    NK(g_nccl.CommInitRank(&H->comm, H->world, id, H->rank));
+    for (int what = 0; what < 3; what++)
+        for (int k = 0; k < 2; k++) {
+            const size_t n = (size_t)sphb_slab_message_doubles(H, what);
+            TRY(dalloc(H, &H->msg_send[what][k], n));
+            TRY(dalloc(H, &H->msg_recv[what][k], n));
+        }
+    TRY(dalloc(H, &H->d_flags, 4));
+    CK(cudaMallocHost((void **)&H->h_flags, 4 * sizeof(int)));
+    CK(cudaStreamSynchronize(H->stream));
+    return SPHB_OK;
+}
+
+// init_particles (setup.cpp:143-228) across the slabs, halo exchanges included
+int sphb_slab_init_particles(sphb_handle *H) {
+    if (!H || !H->comm) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    TRY(sphb_slab_init_lattice(H));
+    if (H->cfg.pressure_calc == SPHB_ADIABATIC) {
+        TRY(native_exchange(H, MSG_BASE));
+        TRY(sphb_density(H, 0));
+        TRY(sphb_slab_prepass(H));
+    }
+    TRY(sphb_ghosts(H, nullptr));
+    TRY(native_exchange(H, MSG_BASE));
+    TRY(sphb_density(H, 1));
+    TRY(sphb_slab_records(H));
+    TRY(native_exchange(H, MSG_RECORDS));
+    return sphb_slab_forces(H);
+}
+
+// SPHSimulation::step_forward (sph_simulation.cpp:55-108) on this rank's slab, nsteps times; every
+// rank of the communicator must make the same call
+int sphb_slab_step(sphb_handle *H, int nsteps) {
+    if (!H || nsteps < 0 || !H->comm) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    for (int k = 0; k < nsteps; k++) {
+        TRY(step_begin(H));
+        int rounds = 0;
+        TRY(native_attempt(H, &rounds));
+        TRY(native_flags(H));
+        if (H->h_flags[1]) {
+            // some rank's drift swapped two neighbours: those ranks sort, everybody repeats the attempt
+            TRY(sphb_slab_resort(H));
+            TRY(native_attempt(H, &rounds));
+            TRY(native_flags(H));
+            if (H->h_flags[1]) { H->err = "x-order still broken after the sort (a particle crossed a slab edge)"; return SPHB_ERR_UNSORTED; }
+        }
+        while (H->h_flags[2] && !H->h_flags[0]) {
+            if (rounds > H->opt.max_sweeps) { H->err = "x-slab ordered sweep did not settle"; return SPHB_ERR_NOT_CONVERGED; }
+            TRY(step_refine(H));
+            TRY(native_exchange(H, MSG_ITERATE));
+            rounds++;
+            TRY(native_flags(H));
+        }
+        if (H->h_flags[0]) {
+            if (H->h_ctl->err_code) return step_error(H);
+            H->err = "a neighbouring slab reported a device error";
+            return H->h_flags[0];
+        }
+        H->rounds_last = rounds;
+        TRY(step_finish(H));
+    }
+    return SPHB_OK;
+}
+
+int sphb_slab_rounds_last(const sphb_handle *H) { return H ? H->rounds_last : -1; }
+
+int sphb_get_counters(sphb_handle *H, sphb_counters *out) {
+    if (!H || !out) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    memset(out, 0, sizeof *out);
+    TRY(read_ctl(H));
+    out->n_alive = H->na;
+    out->n_ghost = wall_ghosts(H);
+    out->steps = H->steps;
+    out->sweeps_total = H->sweeps_total;
+    out->sweeps_last = H->sweeps_last;
+    out->sorts = H->sorts;
+    out->fallbacks = (long long)H->h_ctl->fallbacks;
+    out->h_max = 0.0;
+    { long long b = (long long)H->h_ctl->hmax_bits; memcpy(&out->h_max, &b, sizeof(double)); }
+    out->launches = H->launches;
+    out->force_pairs_mean = H->na ? (double)H->h_ctl->force_pairs / H->na : 0.0;
+    if (H->have_counts) {
+        const int n = H->na;
+        std::vector<int> nw((size_t)n + 2 * H->pad), nb((size_t)n + 2 * H->pad);
+        TRY(sphb_download_counts(H, nw.data(), nb.data(), (int)nw.size()));
+        long long sum = 0;
+        int mn = 1 << 30, mx = 0;
+        for (int i = 0; i < n; i++) {
+            out->newton_hist[std::min(nw[(size_t)i], 11)]++;
+            sum += nb[(size_t)i];
+            mn = std::min(mn, nb[(size_t)i]);
+            mx = std::max(mx, nb[(size_t)i]);
+        }
+        out->nbr_min = mn; out->nbr_max = mx; out->nbr_mean = n ? (double)sum / n : 0.0;
+    }
+    return SPHB_OK;
+}
+
+int sphb_set_profiling(sphb_handle *H, int on) {
+    if (!H) return SPHB_ERR_INVALID;
+    H->profiling = on != 0;
+    return SPHB_OK;
+}
+
+int sphb_get_phase_times(sphb_handle *H, double *ms, long long *launches, int reset) {
+    if (!H) return SPHB_ERR_INVALID;
+    for (int p = 0; p < SPHB_PHASES; p++) {
+        if (ms) ms[p] = H->phase_ms[p];
+        if (launches) launches[p] = H->phase_n[p];
+        if (reset) { H->phase_ms[p] = 0; H->phase_n[p] = 0; }
+    }
+    return SPHB_OK;
+}
+
+
+// ------------------------------------------------------------------------------------
+// sphb_density_static — the density / root-find / omega pass for callers that must not
+// allocate.  It has no counterpart in the reference.
+//
+// Some hosts of this library cannot call cudaMalloc at the point where they need a
+// density pass: applications that hand the whole device to their own arena allocator at
+// start-up (a later cudaMalloc simply fails there), and code inside a latency-critical
+// section where cudaMalloc's device-wide synchronisation would stall every other stream.
+// Every other entry point needs a handle, and sphb_create allocates.  This one needs no
+// handle: the caller passes device pointers for inputs and outputs, and the per-particle
+// work arrays k_density writes besides its outputs (omega of the new and of the old
+// state, packed iteration / neighbour counts) plus the control block live in ONE
+// file-scope device array of fixed size, which every GPU that loads libsphb.so keeps
+// until the process exits (20 MiB + 256 B).
+//
+// Rules that follow from the shared array:
+//   * n is limited to SPHB_STATIC_MAX_PARTICLES; larger calls are refused, nothing runs.
+//   * The array keeps what the previous call left in it.  The control block (error word,
+//     fallback counter, h maximum) is cleared on the stream at the start of every call;
+//     the work arrays are fully rewritten for [0, n) before anything reads them.
+//   * Two calls whose device work overlaps (different streams, or different host threads)
+//     race on the array.  Serialise them.
+//   * The first call on each device looks up the array's device address
+//     (cudaGetSymbolAddress with that device current).  Make that first call before
+//     starting any stream capture.
+// No cudaMalloc / cudaFree / allocating library routine is called on this path.
+namespace {
+constexpr size_t kStaticCtlBytes = 256;
+constexpr size_t kStaticBytes = kStaticCtlBytes + (size_t)SPHB_STATIC_MAX_PARTICLES * (8 + 8 + 4);
+// In host code this name is only a stand-in for the symbol: it is NOT a device address.
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+constexpr int kMaxDevices = 64;
+unsigned char *g_static_ptr[kMaxDevices] = {};   // device address of g_static_scratch, per device
+std::string g_static_err;
+}  // namespace
+
+int sphb_density_static(const double *d_x, const double *d_h, const double *d_rho, int n, double mass,
+                        double h_factor, double limit, int variable_h, double *d_h_out, double *d_rho_out,
+                        void *cuda_stream) {
+    sphb_handle *H = &g_null_handle_for_errors;   // error text is read with sphb_last_error(NULL)
+    if (!d_x || !d_h || !d_rho || !d_h_out || !d_rho_out || n < 1) { H->err = "sphb_density_static: null pointer or n < 1"; return SPHB_ERR_INVALID; }
+    if (n > SPHB_STATIC_MAX_PARTICLES) {
+        char b[200];
+        snprintf(b, sizeof b, "sphb_density_static: n = %d exceeds SPHB_STATIC_MAX_PARTICLES = %d (the static scratch "
+                 "array is fixed-size; use sphb_density on a handle for larger sets)", n, SPHB_STATIC_MAX_PARTICLES);
+        H->err = b;
+        return SPHB_ERR_CAPACITY;
+    }
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) { H->err = "sphb_density_static: device ordinal out of range"; return SPHB_ERR_INVALID; }
+    if (!g_static_ptr[dev]) {
+        // once per device, with that device current: the symbol's address ON THIS DEVICE
+        void *p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_static_scratch));
+        g_static_ptr[dev] = (unsigned char *)p;
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    unsigned char *base = g_static_ptr[dev];
+    Ctl *ctl = (Ctl *)base;
+    double *om_new = (double *)(base + kStaticCtlBytes);
+    double *om_stale = om_new + SPHB_STATIC_MAX_PARTICLES;
+    int *cnt = (int *)(om_stale + SPHB_STATIC_MAX_PARTICLES);
+    CK(cudaMemsetAsync(ctl, 0, sizeof(Ctl), st));   // GL = GR = 0 (no ghosts), no error, hmax = 0
+    DensityArgs A;
+    A.x = d_x; A.m = nullptr; A.h = d_h; A.rho = d_rho; A.P = nullptr;
+    A.hn = d_h_out; A.rhon = d_rho_out; A.omn = om_new; A.oms = om_stale; A.Pn = nullptr;
+    A.rec = nullptr; A.gsum = nullptr;
+    A.cnt = cnt; A.ctl = ctl; A.pad = 0; A.na = n;
+    A.limit = limit; A.hfac = h_factor; A.m0 = mass;
+    A.root_ghosts = 0; A.root_alive = 1; A.check_old = 0;
+    const int grid = nblk(n, kTile);
+    if (variable_h) k_density<true, true><<<grid, kTile, 0, st>>>(A);
+    else k_density<false, true><<<grid, kTile, 0, st>>>(A);
+    CK(cudaGetLastError());
+    Ctl host_ctl;   // pageable stack memory: the copy allocates nothing
+    CK(cudaMemcpyAsync(&host_ctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (host_ctl.err_code != 0) {
+        char b[256];
+        snprintf(b, sizeof b, "%s (particle %d)", err_text(host_ctl.err_code), host_ctl.err_particle);
+        H->err = b;
+        return host_ctl.err_code;
+    }
+    return SPHB_OK;
+}
+
+}  // extern "C"

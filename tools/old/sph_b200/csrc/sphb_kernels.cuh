@@ -1,0 +1,1141 @@
+// sphb_kernels.cuh — device code of libsphb.so (sm_100a, FP64 SIMT).
+//
+// Layout.  All per-particle arrays are structure-of-arrays in HBM, kept x-SORTED, with
+// a pad of `pad` slots on either side of the alive block:
+//
+//     [ 0 .. pad-GL ) unused | [pad-GL .. pad) left ghosts | [pad .. pad+NA) alive |
+//     [pad+NA .. pad+NA+GR) right ghosts | unused
+//
+// so every neighbour sum is a contiguous window scan over [lo, hi) = [pad-GL, pad+NA+GR)
+// with no special case for ghosts (and, across GPUs, none for halo particles, which use
+// the same pads).  `idx` carries the particle's ORIGINAL array index (the reference's
+// sweep order, sph_simulation.cpp:94, is by array index, not by x: SURVEY.md F9); ghost
+// slots have bit 31 set so they compare greater than every alive index.
+//
+// Arithmetic.  The file is compiled with -fmad=false: nothing is contracted implicitly,
+// fused multiply-adds are written out with fma().  Where the reference's result decides
+// a COUNT (ghost predicate, neighbour predicate, kick/drift that feeds them) the
+// reference's expression is evaluated operation by operation with IEEE rounding.
+#pragma once
+#include <cooperative_groups.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cg = cooperative_groups;
+
+namespace sphb {
+
+constexpr double kEps = 1e-8;          // CALC_EPSILON, define.hpp:25
+constexpr double kGamma = 5.0 / 3.0;   // GAMMA, define.hpp:32
+constexpr int kMaxIterNR = 10;         // H_MAX_ITER_NR, define.hpp:39
+constexpr int kMaxIterBS = 1000;       // H_MAX_ITER_BS, define.hpp:41
+constexpr double kHEps = 1e-4;         // H_EPSILON, define.hpp:43
+constexpr double kRadius = 2.5;        // KERNEL_RADIUS, kernel.hpp:12
+constexpr double kSigma = 1.0 / 24.0;  // kernel.cpp:16
+constexpr unsigned kGhostBit = 0x80000000u;
+
+constexpr int kTile = 256;             // particles per CTA tile
+
+enum ErrCode {
+    E_OK = 0, E_CAPACITY = 3, E_NEGATIVE_H = 4, E_LOW_DENSITY = 5, E_GHOST_ZERO_H = 6,
+    E_ZERO_DERIVATIVE = 7, E_NOT_FINITE = 8, E_NO_BRACKET = 9, E_NOT_CONVERGED = 10,
+    E_UNSORTED = 11, E_HALO = 13
+};
+
+// Device control block (one per handle), read back by the host at sync points.
+struct Ctl {
+    int GL, GR;                    // ghosts currently in the left / right pad
+    int ncand;                     // ghost candidates appended this step
+    int unsorted;                  // order check failed
+    int err_code, err_particle;    // first error wins
+    unsigned long long hmax_bits;  // max over every h (old and new) in [lo,hi), as ordered bits
+    unsigned long long fallbacks;  // bisection fallbacks taken
+    int nwork[3];                  // tiles in the work list of the sweep whose stamp is k mod 3
+    int nwork_peak;                // largest work list of the current step (sizes the next step's refinement grid)
+    int sweeps_used;               // force sweeps the last step needed
+    int epoch_cur;                 // stamp of the most recent force sweep (handed from launch to launch)
+    int halo_left, halo_right;     // the pad on that side holds another slab's particles, not wall ghosts
+    int halo_changed;              // an incoming halo iterate differed from the copy held here
+    unsigned long long force_pairs; // (i,j) pairs evaluated by the first force sweep (self included)
+};
+
+__device__ __forceinline__ void raise(Ctl *ctl, int code, int particle) {
+    if (atomicCAS(&ctl->err_code, 0, code) == 0) ctl->err_particle = particle;
+}
+
+// ------------------------------------------------------------------------------------
+// Arithmetic of the hot loops: the M5 quartic spline (kernel.cpp:14-64) in "r space".
+// With t_k = a_k h - r (a_k = 5/2, 3/2, 1/2) and T_k = max(t_k, 0) the pieces are T_k / h, so
+//     w(q)            = sigma / h^4 * [ T1^4 - 5 T2^4 + 10 T3^4 ]
+//     w(q) + q w'(q)  = sigma / h^4 * [ T1^3 (a1 h - 5 r) - 5 T2^3 (a2 h - 5 r) + 10 T3^3 (a3 h - 5 r) ]
+//     w'(q) / h^2     = sigma / h^5 * [ -4 T1^3 + 20 T2^3 - 40 T3^3 ]
+// — no division and no q per neighbour.  An FP64 max costs three instructions on sm_100a
+// (DSETP + 2 SEL); s = t + |t| = 2 max(t, 0) is ONE DADD and exact, and the powers of two it
+// brings in are folded into the coefficients (exactly).
+__device__ __forceinline__ double clamp2(double t) { return t + fabs(t); }   // 2 * max(t, 0)
+
+// [T1^3 - 5 T2^3 + 10 T3^3] = -(1/4) h^5 / sigma * w'(q)/h^2 for smoothing length h at distance r >= 0.
+// The FP64 pipe is what bounds the force pass, so the pieces are entered by branching on the SIGN
+// of t_k (an integer test of the high word, off the FP64 pipe) instead of clamping: a neighbour in
+// the outer shell costs 4 FP64 operations here, not 15.  Neighbouring lanes hold neighbouring
+// particles with nearly the same h and spacing, so the branches rarely diverge.
+__device__ __forceinline__ double dpoly_from(double t1, double r, double h, double k2, double k3) {
+    double p = 0.0;
+    if (__double2hiint(t1) >= 0) {
+        p = (t1 * t1) * t1;
+        const double t2 = fma(k2, h, -r);
+        if (__double2hiint(t2) >= 0) {
+            p = fma(-5.0, (t2 * t2) * t2, p);
+            const double t3 = fma(k3, h, -r);
+            if (__double2hiint(t3) >= 0) p = fma(10.0, (t3 * t3) * t3, p);
+        }
+    }
+    return p;
+}
+constexpr double kGradC = -4.0 * kSigma;   // w'(q)/h^2 = kGradC / h^5 * dpoly(r, h)
+
+// What the density pass leaves per particle for the force pass: everything a pair needs from
+// its neighbour without a division.
+struct __align__(32) Rec {
+    double h;     // smoothing length
+    double c5;    // -4 sigma / h^5
+    double rho;   // density
+    double kap;   // 1 / (rho * omega):  P / (rho^2 omega) = (gamma - 1) u kap (adiabatic), kap (isothermal)
+};
+
+struct __align__(64) Rec2 { Rec A, B; };   // new state (as seen once the sweep has passed) / old state
+
+constexpr int kDHalo = 64;    // density pass: x staged on each side of a tile
+constexpr int kFHalo = 32;    // force pass: neighbour state staged on each side of a tile
+
+// ------------------------------------------------------------------------------------
+// One evaluation of the two density-pass sums at trial smoothing length h over the sorted
+// window, self included:
+//   Sw = sum_j [T1^4 - 5 T2^4 + 10 T3^4]           so that  sum_j w(q_j)              = sigma/h^4 Sw
+//   Sg = sum_j m_j [T1^3 (a1 h - 5 r) - ...]        so that  sum_j m_j (w + q w')(q_j) = sigma/h^4 Sg
+//   Sgr = sum_j m_j sign(x_i - x_j) [T1^3 - 5 T2^3 + 10 T3^3]   so that  sum_j m_j gradW_ij(h) = -4 sigma/h^5 Sgr
+//   cnt = #{ j : |x_i - x_j| / h < 2.5 }            with the reference's IEEE division (kernel.cpp:31)
+// sx is the staged window, sx[k] = x[wbase + k] for 0 <= k < wn, with +-INF sentinels at
+// sx[-1] and sx[wn]; a scan that runs off the staged part goes on in global memory.  The scan
+// stops at the first particle outside the support: the array is x-sorted, so every farther
+// one is outside as well.
+// one neighbour at distance r (0 <= r < 2.5 h): adds its terms to sw, sg
+template <bool UM>
+__device__ __forceinline__ void density_term(double r, double a1, double a2, double a3, double mj, double &sw,
+                                             double &sg, double &sgr) {
+    const double t1 = a1 - r;
+    const double c1 = (t1 * t1) * t1;
+    const double r5 = 5.0 * r;
+    sw = fma(c1, t1, sw);
+    double g = c1 * (a1 - r5);
+    double d = c1;                                 // T1^3 - 5 T2^3 + 10 T3^3: the gradient's polynomial
+    const double t2 = a2 - r;
+    if (__double2hiint(t2) >= 0) {                 // sign tests run off the FP64 pipe (see dpoly_from)
+        const double c2 = -5.0 * ((t2 * t2) * t2);
+        sw = fma(c2, t2, sw);
+        g = fma(c2, a2 - r5, g);
+        d += c2;
+        const double t3 = a3 - r;
+        if (__double2hiint(t3) >= 0) {
+            const double c3 = 10.0 * ((t3 * t3) * t3);
+            sw = fma(c3, t3, sw);
+            g = fma(c3, a3 - r5, g);
+            d += c3;
+        }
+    }
+    if (UM) { sg += g; sgr += d; } else { sg = fma(mj, g, sg); sgr = fma(mj, d, sgr); }
+}
+
+// one side (DIR = -1 left, +1 right) of the scan around sorted slot s
+template <bool UM, int DIR>
+__device__ __forceinline__ void density_side(Ctl *ctl, bool own, const double *sx, int wbase, int wn, const double *__restrict__ gx,
+                                             const double *__restrict__ m, int s, int lo, int hi, double xi,
+                                             double h, double a1, double a2, double a3, double r_in, double &sw,
+                                             double &sg, double &sgr, int &c) {
+    int k = s - wbase + DIR;
+    double r;
+#pragma unroll 1
+    while (true) {                                  // staged part; the +-INF sentinels end it
+        r = DIR > 0 ? (sx[k] - xi) : (xi - sx[k]);
+        if (!(r < r_in)) break;
+        c++;
+        density_term<UM>(r, a1, a2, a3, UM ? 0.0 : __ldg(m + wbase + k), sw, sg, sgr);
+        k += DIR;
+    }
+    // From here on r >= r_in (x is sorted): only particles within rounding of the support edge can
+    // still count (kernel.cpp:31 decides with an IEEE division); they contribute < 1e-57 h^4.
+#pragma unroll 1
+    while (k >= 0 && k < wn) {
+        if (!(r / h < kRadius)) return;
+        c++;
+        k += DIR;
+        r = DIR > 0 ? (sx[k] - xi) : (xi - sx[k]);
+    }
+    // rare: the scan ran off the staged part (more than kDHalo neighbours on this side)
+    int j = wbase + k;
+#pragma unroll 1
+    for (; j >= lo && j < hi; j += DIR) {
+        r = DIR > 0 ? (__ldg(gx + j) - xi) : (xi - __ldg(gx + j));
+        if (r < r_in) {
+            c++;
+            density_term<UM>(r, a1, a2, a3, UM ? 0.0 : __ldg(m + j), sw, sg, sgr);
+        } else if (r / h < kRadius) {
+            c++;
+        } else {
+            return;
+        }
+    }
+    // every particle on this side lies inside the support: fine next to a wall, but on a slab
+    // edge it means the halo is thinner than the kernel reaches
+    if (own && (DIR < 0 ? ctl->halo_left : ctl->halo_right)) raise(ctl, E_HALO, s);
+}
+
+template <bool UM>
+__device__ __forceinline__ void density_sums(Ctl *ctl, bool own, const double *sx, int wbase, int wn, const double *__restrict__ gx,
+                                             const double *__restrict__ m, int s, int lo, int hi, double xi,
+                                             double h, double &Sw, double &Sg, double &Sgr, int &cnt) {
+    const double a1 = 2.5 * h, a2 = 1.5 * h, a3 = 0.5 * h;
+    const double r_in = a1 * (1.0 - 0x1p-48);     // below: certainly inside; from there on decide exactly
+    const double h2 = h * h;
+    const double self = 14.375 * (h2 * h2);       // r = 0: (5/2)^4 - 5 (3/2)^4 + 10 (1/2)^4, times h^4
+    double sw = self, sg = UM ? self : self * __ldg(m + s);
+    int c = 1;
+    double grl = 0.0, grr = 0.0;
+    density_side<UM, -1>(ctl, own, sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, grl, c);
+    density_side<UM, +1>(ctl, own, sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, grr, c);
+    Sw = sw;
+    Sg = sg;
+    Sgr = grl - grr;                              // gradW carries sign(x_i - x_j): + for left neighbours
+    cnt = c;
+}
+
+struct DensityArgs {
+    const double *x, *m, *h, *rho, *P;
+    double *hn, *rhon, *Pn;
+    double *omn, *oms;   // omega for the new / the old (h, rho) at the new positions; may be null
+    Rec2 *rec;           // force-pass records of the new and the old state; may be null
+    double *gsum;        // sum_j m_j gradW_ij(h_i^new): the acceleration's own-h term; null iff rec is null
+    int *cnt;            // (newton_iters << 24) | neighbour count
+    Ctl *ctl;
+    int pad, na;
+    double limit, hfac, m0;
+    int root_ghosts;     // 1: ghosts are root-found too (t = 0, setup.cpp:218-220)
+    int root_alive;      // 0: omega-only pass (keeps h, rho; used by sphb_forces / sphb_omega)
+    int check_old;       // 1: the old (h, rho) state is also seen by force sums (step path)
+};
+
+// Fused density + variable-h root-find + omega, one thread per
+// particle.  Newton follows rootfind_h (smoothing_length.cpp:191-259) and GSL's
+// newton/test_delta step for step: same start value, same
+// update, same stop test, same iteration cap, then the bisection fallback (:134-188).
+// The last Newton evaluation is at the returned h, so its sums ARE the final density
+// (calculators.cpp:45) and omega_new; the first evaluation is at the old h, so its
+// derivative sum gives omega_stale = calc_omega(old h, old rho) at the new positions.
+// With f(h) = m_i sigma Sw / h^5 - m_i hf / h and f'(h) = -sigma Sg / h^6 + m_i hf / h^2.
+template <bool VARH, bool UM>
+__global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
+    __shared__ double sxs[kTile + 2 * kDHalo + 2];
+    double *sx = sxs + 1;
+    Ctl *ctl = A.ctl;
+    const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
+    const int t0 = blockIdx.x * kTile;          // grid covers [0, pad + na + pad)
+    if (t0 >= hi || t0 + kTile <= lo) return;
+    const int wbase = max(t0 - kDHalo, lo);
+    const int wn = min(t0 + kTile + kDHalo, hi) - wbase;
+    for (int k = threadIdx.x; k < wn; k += kTile) sx[k] = A.x[wbase + k];
+    if (threadIdx.x == 0) { sx[-1] = -INFINITY; sx[wn] = INFINITY; }
+    __syncthreads();
+
+    const int s = t0 + threadIdx.x;
+    double hloc = 0.0;
+    // pad slots that hold another slab's particles get everything from their owner
+    const bool halo_slot = (s < A.pad && ctl->halo_left) || (s >= A.pad + A.na && ctl->halo_right);
+    if (s >= lo && s < hi && !halo_slot) {
+        const bool is_pad = (s < A.pad) || (s >= A.pad + A.na);
+        const bool do_root = VARH && (is_pad ? A.root_ghosts : A.root_alive);
+        const double xi = sx[s - wbase];
+        const double mi = UM ? A.m0 : A.m[s];
+        const double msig = UM ? kSigma : 1.0;   // with uniform masses Sg lacks the factor m_j = m0
+        const double hold = A.h[s], rhoold = A.rho[s];
+        const int npart = A.na + ctl->GL + ctl->GR;
+        double hnew = hold, rhonew = rhoold, om_new = 1.0, om_stale = 1.0;
+        int iters = 0, cnt = 0;
+        double Sw, Sg, Sgr = 0.0;
+#define SPHB_EVAL(H_, F_, DF_, DSUM_)                                                           \
+    {                                                                                           \
+        density_sums<UM>(ctl, !is_pad, sx, wbase, wn, A.x, A.m, s, lo, hi, xi, (H_), Sw, Sg, Sgr, cnt); \
+        const double ih_ = 1.0 / (H_), ih2_ = ih_ * ih_, ih4_ = ih2_ * ih2_;                    \
+        const double rho_ = mi * (kSigma * (Sw * (ih4_ * ih_)));                                \
+        F_ = rho_ - mi * A.hfac * ih_;                                                          \
+        DSUM_ = UM ? -(mi * (kSigma * (Sg * (ih4_ * ih2_)))) : -(kSigma * (Sg * (ih4_ * ih2_))); \
+        DF_ = DSUM_ + mi * A.hfac * ih2_;                                                       \
+        rho_cur = rho_;                                                                         \
+    }
+        (void)msig;
+        if (VARH) {
+            const double x0 = hold > kEps ? hold : A.hfac * (2 * A.limit / (npart - 1));
+            double f, df, dsum, rho_cur;
+            SPHB_EVAL(x0, f, df, dsum);
+            om_stale = 1.0 - dsum * (-hold / rhoold);
+            if (do_root) {
+                double xcur = x0;
+                bool cont = true;
+#pragma unroll 1
+                while (cont && iters < kMaxIterNR) {
+                    iters++;
+                    if (df == 0.0) { raise(ctl, E_ZERO_DERIVATIVE, s); break; }
+                    const double xn = xcur - f / df;
+                    SPHB_EVAL(xn, f, df, dsum);
+                    if (!isfinite(f) || !isfinite(df)) { raise(ctl, E_NOT_FINITE, s); break; }
+                    const double xprev = xcur;
+                    xcur = xn;
+                    cont = !(fabs(xcur - xprev) < kHEps * fabs(xcur) || xcur == xprev);
+                }
+                if (cont && ctl->err_code == 0) {
+                    // bisection fallback on [1e-8, 2 limit], gsl_root_test_interval rel 1e-4
+                    // (its bracket end 2*limit sums over the whole domain: a slab cannot evaluate it)
+                    if (ctl->halo_left | ctl->halo_right) raise(ctl, E_HALO, s);
+                    atomicAdd(&ctl->fallbacks, 1ull);
+                    double xl = kEps, xh = 2 * A.limit, fl, fh, dfx, dsx;
+                    int c2 = cnt;
+                    SPHB_EVAL(xl, fl, dfx, dsx);
+                    SPHB_EVAL(xh, fh, dfx, dsx);
+                    double root = 0.5 * (xl + xh);
+                    if (!isfinite(fl) || !isfinite(fh)) raise(ctl, E_NOT_FINITE, s);
+                    else if ((fl < 0.0 && fh < 0.0) || (fl > 0.0 && fh > 0.0)) raise(ctl, E_NO_BRACKET, s);
+                    else {
+                        int it = 0;
+                        bool go = true;
+#pragma unroll 1
+                        while (go && it < kMaxIterBS) {
+                            it++;
+                            if (fl == 0.0) { root = xl; xh = xl; }
+                            else if (fh == 0.0) { root = xh; xl = xh; }
+                            else {
+                                const double mid = (xl + xh) / 2.0;
+                                double fm;
+                                SPHB_EVAL(mid, fm, dfx, dsx);
+                                if (!isfinite(fm)) { raise(ctl, E_NOT_FINITE, s); break; }
+                                if (fm == 0.0) { root = mid; xl = mid; xh = mid; }
+                                else if ((fl > 0.0 && fm < 0.0) || (fl < 0.0 && fm > 0.0)) {
+                                    root = 0.5 * (xl + mid); xh = mid; fh = fm;
+                                } else {
+                                    root = 0.5 * (mid + xh); xl = mid; fl = fm;
+                                }
+                            }
+                            double smallest = 0.0;
+                            if ((xl > 0.0 && xh > 0.0) || (xl < 0.0 && xh < 0.0)) smallest = fmin(fabs(xl), fabs(xh));
+                            go = !(fabs(xh - xl) < kHEps * smallest);
+                        }
+                    }
+                    (void)c2;
+                    xcur = root;
+                    SPHB_EVAL(xcur, f, df, dsum);
+                }
+                if (xcur < 0) raise(ctl, E_NEGATIVE_H, s);
+                hnew = xcur;
+                rhonew = rho_cur;
+                om_new = 1.0 - dsum * (-hnew / rhonew);
+            } else {
+                om_new = om_stale;   // particle keeps its stored h, rho: omega for those
+            }
+        } else {
+            double f, df, dsum, rho_cur;
+            SPHB_EVAL(hold, f, df, dsum);
+            (void)f; (void)df; (void)dsum;
+            if (is_pad ? A.root_ghosts : A.root_alive) rhonew = rho_cur;
+        }
+#undef SPHB_EVAL
+        A.hn[s] = hnew;
+        A.rhon[s] = rhonew;
+        if (A.omn) { A.omn[s] = om_new; A.oms[s] = om_stale; }
+        if (A.rec) {
+            // c5 = -4 sigma / h^5 and kap = 1 / (rho omega): the only divisions the force pass would need
+            const double ihn = 1.0 / hnew, ihn2 = ihn * ihn;
+            Rec2 r2;
+            r2.A.h = hnew; r2.A.c5 = kGradC * ((ihn2 * ihn2) * ihn); r2.A.rho = rhonew; r2.A.kap = 1.0 / (rhonew * om_new);
+            r2.B = r2.A;
+            if (VARH && A.check_old) {
+                const double iho = 1.0 / hold, iho2 = iho * iho;
+                r2.B.h = hold; r2.B.c5 = kGradC * ((iho2 * iho2) * iho); r2.B.rho = rhoold; r2.B.kap = 1.0 / (rhoold * om_stale);
+            } else if (A.check_old) {
+                r2.B.rho = rhoold; r2.B.kap = 1.0 / rhoold;      // fixed h: omega = 1, h unchanged
+            }
+            A.rec[s] = r2;
+            // Sgr belongs to the LAST evaluation, which was at hnew (or at the stored h when nothing was root-found)
+            A.gsum[s] = (UM ? mi : 1.0) * (r2.A.c5 * Sgr);
+        }
+        if (A.root_alive || A.root_ghosts) A.cnt[s] = (iters << 24) | (cnt & 0xffffff);
+        if (is_pad && A.Pn != A.P) A.Pn[s] = A.P[s];
+        // ensure_nonzero_density (calculators.cpp:174-186) guards every particle a force sum
+        // touches, in whichever state (new, or old when check_old) it will be seen
+        if (rhonew < kEps || (A.check_old && rhoold < kEps)) raise(ctl, E_LOW_DENSITY, s);
+        hloc = fmax(hnew, hold);
+    }
+    // block max of h -> global upper bound for the force pass window
+    __shared__ double smax[kTile / 32];
+    for (int o = 16; o > 0; o >>= 1) hloc = fmax(hloc, __shfl_xor_sync(0xffffffffu, hloc, o));
+    if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = hloc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double mx = smax[0];
+        for (int k = 1; k < kTile / 32; k++) mx = fmax(mx, smax[k]);
+        atomicMax(&ctl->hmax_bits, (unsigned long long)__double_as_longlong(mx));
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// Force pass: acceleration (calculators.cpp:63-129) and du/dt (:192-213) fused, one
+// thread per alive particle, neighbours "as seen by i" (SURVEY.md Appendix A.6):
+// state A (new h, rho, omega and the current iterate of the fully-kicked v, u) for
+// particles the reference's sweep has already updated when it reaches i, state B
+// (last step's h, rho, omega_stale, half-kicked v, u) for the others and for ghosts.
+struct ForceArrays {
+    const double *x;
+    const unsigned *idx;
+    const double *m;
+    const Rec2 *rec;
+    const double *gsum;        // sum_j m_j gradW_ij(h_i) from the density pass
+    const double *vA, *uA;     // current iterate of the fully kicked v, u (read with .cg: other CTAs update it)
+    const double *vB, *uB;     // half-kicked base state
+};
+
+enum { SEL_INDEX = 0, SEL_ALIVE = 1, SEL_ALL_A = 2 };
+
+struct SweepArgs {
+    ForceArrays F;
+    const double *Pstale;   // stored pressure of the previous force pass
+    double *Pout;           // new stored pressure
+    double *a, *du;         // outputs
+    double *vn, *un;        // fully-kicked outputs (iterate)
+    const double *vh, *uh;  // half-kicked base state of i itself
+    int *dirty;             // per-tile stamp: epoch of the last sweep that changed something in range
+    int *wl[3];             // work lists of tiles, by sweep stamp mod 3
+    Ctl *ctl;
+    int pad, na;
+    double m0, half_dt;
+    int epoch;              // stamp of this sweep
+    int kick;               // 0: t = 0 semantics (no kick, calculators only)
+};
+
+// per-thread invariants of one force evaluation
+template <bool ADIA>
+struct Own {
+    double x, h, rho, v, PrRho, c_ac, c_ec, P;
+    unsigned idx;
+    __device__ __forceinline__ void set(double xi, unsigned idxi, const Rec &r, double vi, double ui, double Pstale) {
+        x = xi; idx = idxi; h = r.h; rho = r.rho; v = vi;
+        P = ADIA ? ((kGamma - 1) * ui) * r.rho : r.rho;                 // calculators.cpp:131-137
+        c_ac = ADIA ? sqrt(kGamma * Pstale / r.rho) : 1.0;              // stale stored pressure
+        c_ec = ADIA ? sqrt(kGamma * P / r.rho) : 1.0;                   // fresh pressure
+        PrRho = ADIA ? ((kGamma - 1) * ui) * r.kap : r.kap;             // P_i / (rho_i^2 omega_i)
+    }
+};
+
+// One (i, j) pair; ar = |x_i - x_j| >= 0 and the sign of the gradient is applied by the caller per
+// side.  The acceleration's first term, gradW(h_i) P_i/(rho_i^2 om_i), does not depend on j's state:
+// its sum over j comes from the density pass (gsum).  accA gathers m_j [gradW(h_j) P_j/(rho_j^2 om_j)
+// + gradW(hbar) Pi_ij(c_ac)], accE gathers m_j v_ij gradW(hbar) [P_i/(rho_i^2 om_i) + Pi_ij(c_ec)/2],
+// both without the sign.  dir = +1 for a left neighbour (x_i - x_j = +ar), -1 for a right one.
+// Everything is written with hs = h_i + h_j = 2 hbar.
+template <bool ADIA, bool UM>
+__device__ __forceinline__ bool pair_terms(const Own<ADIA> &o, double ar, double dir, const Rec &rj, double vj,
+                                           double uj, double mj, double &accA, double &accE) {
+    const double hs = o.h + rj.h;
+    const double t1j = fma(2.5, rj.h, -ar), t1b = fma(1.25, hs, -ar);
+    if ((__double2hiint(t1j) & __double2hiint(t1b)) < 0) return false;   // beyond 2.5 h_j and 2.5 hbar
+    const double rs = o.rho + rj.rho;
+    const double D = fma(ar, ar, 0.0025 * (hs * hs));        // r^2 + 0.01 hbar^2
+    // one reciprocal serves 1/hbar, 1/D and 1/(rho_i + rho_j)
+    const double DP = D * rs;
+    const double R = 1.0 / (hs * DP);
+    const double ihs = R * DP;
+    const double t = R * hs;              // 1 / (D rs)
+    const double iD = t * rs;
+    const double irs = t * D;
+    const double ihs2 = ihs * ihs;
+    // gradW(hbar) without its sign: -4 sigma / hbar^5 * poly = -128 sigma / hs^5 * poly
+    const double gb = dpoly_from(t1b, ar, hs, 0.75, 0.25) * ((32.0 * kGradC) * ((ihs2 * ihs2) * ihs));
+    const double PrRho_j = ADIA ? ((kGamma - 1) * uj) * rj.kap : rj.kap;
+    const double gj = dpoly_from(t1j, ar, rj.h, 1.5, 0.5) * (rj.c5 * PrRho_j);
+    const double v_ij = o.v - vj;
+    const double dot = v_ij * (dir * ar);
+    // artificial viscosity (calculators.cpp:148-172): alpha = 1, beta = 2, eta^2 = 0.01 hbar^2
+    double visc_ac = 0.0, visc_ec = 0.0;
+    if (!(dot > 0)) {
+        const double mu = ((0.5 * hs) * dot) * iD;
+        const double two_mu2 = 2.0 * (mu * mu);
+        const double irho = 2.0 * irs;               // 1 / ((rho_i + rho_j) / 2)
+        visc_ac = fma(-o.c_ac, mu, two_mu2) * irho;
+        visc_ec = fma(-o.c_ec, mu, two_mu2) * irho;
+    }
+    const double ta = fma(gb, visc_ac, gj);
+    const double te = (v_ij * gb) * fma(0.5, visc_ec, o.PrRho);
+    if (UM) { accA += ta; accE += te; }
+    else { accA = fma(mj, ta, accA); accE = fma(mj, te, accE); }
+    return true;
+}
+
+// Shared-memory image of a tile and its surroundings for the force pass.
+struct ForceSmem {
+    double x[kTile + 2 * kFHalo + 2];
+    // records split in 16-byte halves so that a warp's LDS.128 is conflict-free; [0] = new state A, [1] = old state B
+    double2 hc[2][kTile + 2 * kFHalo];   // (h, c5)
+    double2 rk[2][kTile + 2 * kFHalo];   // (rho, kap)
+    double vA[kTile + 2 * kFHalo], uA[kTile + 2 * kFHalo];
+    double vB[kTile + 2 * kFHalo], uB[kTile + 2 * kFHalo];
+    unsigned idx[kTile + 2 * kFHalo];
+};
+
+template <bool VOL>
+__device__ __forceinline__ double ldv(const double *p) { return VOL ? __ldcg(p) : __ldg(p); }
+
+template <int SEL>
+__device__ __forceinline__ bool sees_new_state(unsigned idxj, unsigned idxi) {
+    if (SEL == SEL_INDEX) return idxj < idxi;            // the reference's sweep has already updated j
+    if (SEL == SEL_ALIVE) return !(idxj & kGhostBit);
+    return true;
+}
+
+// All neighbours on one side (DIR = -1: left, x_j <= x_i; +1: right) of particle `o`, staged part
+// first, then (rarely) global memory.  gradW carries sign(x_i - x_j) (calculators.cpp:17-27): the
+// unsigned sums of this side enter a with -DIR... i.e. a -= accA on the left, a += accA on the right,
+// and du/dt with the opposite signs.  `jend` receives the farthest slot within reach.
+template <int SEL, bool ADIA, bool UM, bool FIRST, int DIR>
+__device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &S, const Own<ADIA> &o, int ks,
+                                           int wbase, int wn, int lo, int hi, double reach, double &a_sum,
+                                           double &e_sum, int &npairs, int &jend) {
+    const double *sx = S.x + 1;
+    const double dir = DIR > 0 ? -1.0 : 1.0;      // sign of x_i - x_j
+    double accA = 0.0, accE = 0.0;
+    int k = ks + DIR;
+#pragma unroll 1
+    while (true) {
+        const double ar = DIR > 0 ? (sx[k] - o.x) : (o.x - sx[k]);
+        if (!(ar < reach)) break;                 // also the +-INF sentinels
+        const bool useA = sees_new_state<SEL>(S.idx[k], o.idx);
+        const int sel = useA ? 0 : 1;
+        const double2 hc = S.hc[sel][k], rk = S.rk[sel][k];
+        Rec rj;
+        rj.h = hc.x; rj.c5 = hc.y; rj.rho = rk.x; rj.kap = rk.y;
+        const double vj = (useA && !FIRST) ? S.vA[k] : S.vB[k];
+        const double uj = (useA && !FIRST) ? S.uA[k] : S.uB[k];
+        const double mj = UM ? 0.0 : __ldg(A.F.m + wbase + k);
+        if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
+        k += DIR;
+    }
+    int j = wbase + k;                            // first particle not handled above
+    if ((k < 0 || k >= wn) && j >= lo && j < hi) {
+        // rare: the reach extends beyond the staged halo — continue in global memory
+#pragma unroll 1
+        for (; j >= lo && j < hi; j += DIR) {
+            const double xj = __ldg(A.F.x + j);
+            const double ar = DIR > 0 ? (xj - o.x) : (o.x - xj);
+            if (!(ar < reach)) break;
+            const bool useA = sees_new_state<SEL>(__ldg(A.F.idx + j), o.idx);
+            const Rec rj = useA ? A.F.rec[j].A : A.F.rec[j].B;
+            const double vj = (useA && !FIRST) ? ldv<true>(A.F.vA + j) : __ldg(A.F.vB + j);
+            const double uj = (useA && !FIRST) ? ldv<true>(A.F.uA + j) : __ldg(A.F.uB + j);
+            const double mj = UM ? 0.0 : __ldg(A.F.m + j);
+            if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
+        }
+    }
+    if ((j < lo || j >= hi) && (DIR < 0 ? A.ctl->halo_left : A.ctl->halo_right)) raise(A.ctl, E_HALO, wbase + ks);
+    jend = j - DIR;
+    a_sum = DIR > 0 ? (a_sum + accA) : (a_sum - accA);
+    e_sum = DIR > 0 ? (e_sum - accE) : (e_sum + accE);
+}
+
+// Evaluate one tile: stage, compute a, du/dt (and the kick), store.  Returns through
+// `changed_any` whether any particle's kicked (v, u) differs from what was stored before.
+// FIRST: sweep 1 of a step (vA == vB: everybody is seen half-kicked, outputs always stored).
+template <int SEL, bool ADIA, bool UM, bool FIRST>
+__device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo, int hi, double Hb,
+                                           int epoch, bool &changed_any, int &npairs_out) {
+    __shared__ ForceSmem S;
+    const int t0 = A.pad + tile * kTile;
+    const int tend = min(t0 + kTile, A.pad + A.na);
+    const int wbase = max(t0 - kFHalo, lo);
+    const int wn = min(t0 + kTile + kFHalo, hi) - wbase;
+    double *sx = S.x + 1;
+    __syncthreads();                                   // previous tile's readers are done
+    for (int k = threadIdx.x; k < wn; k += kTile) {
+        const int j = wbase + k;
+        sx[k] = A.F.x[j];
+        S.idx[k] = A.F.idx[j];
+        {
+            const Rec2 r2 = A.F.rec[j];
+            S.hc[0][k] = make_double2(r2.A.h, r2.A.c5); S.rk[0][k] = make_double2(r2.A.rho, r2.A.kap);
+            S.hc[1][k] = make_double2(r2.B.h, r2.B.c5); S.rk[1][k] = make_double2(r2.B.rho, r2.B.kap);
+        }
+        S.vB[k] = __ldg(A.F.vB + j);
+        S.uB[k] = __ldg(A.F.uB + j);
+        if (!FIRST) { S.vA[k] = ldv<true>(A.F.vA + j); S.uA[k] = ldv<true>(A.F.uA + j); }
+    }
+    if (threadIdx.x == 0) { sx[-1] = -INFINITY; sx[wn] = INFINITY; }
+    __syncthreads();
+
+    const int s = t0 + threadIdx.x;
+    bool changed = false;
+    int npairs = 0;
+    if (s < tend) {
+        const int ks = s - wbase;
+        Own<ADIA> o;
+        const double vi = A.vh[s], ui = A.uh[s];
+        {
+            Rec ro;
+            ro.h = S.hc[0][ks].x; ro.c5 = S.hc[0][ks].y; ro.rho = S.rk[0][ks].x; ro.kap = S.rk[0][ks].y;
+            o.set(sx[ks], S.idx[ks], ro, vi, ui, A.Pstale[s]);
+        }
+        const double reach = kRadius * Hb;
+        double a_sum = 0.0, e_sum = 0.0;
+        int jmin = s, jmax = s;
+        npairs = 1;   // self: its energy term is evaluated by the reference too (and is exactly 0)
+        force_side<SEL, ADIA, UM, FIRST, -1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmin);
+        force_side<SEL, ADIA, UM, FIRST, +1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmax);
+        if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
+        a_sum = fma(-o.PrRho, A.F.gsum[s], a_sum);        // - P_i/(rho_i^2 om_i) sum_j m_j gradW_ij(h_i)
+        if (!A.kick) {
+            A.a[s] = a_sum;
+            A.du[s] = e_sum;
+            A.Pout[s] = o.P;
+        } else {
+            // second half-kick, sph_simulation.cpp:105-106, operation by operation
+            const double vf = __dadd_rn(vi, __dmul_rn(a_sum, A.half_dt));
+            const double uf = __dadd_rn(ui, __dmul_rn(e_sum, A.half_dt));
+            if (FIRST) {
+                A.a[s] = a_sum; A.du[s] = e_sum; A.Pout[s] = o.P;
+                A.vn[s] = vf; A.un[s] = uf;
+                // later-index neighbours used (vh, uh) as their guess for this particle
+                changed = (__double_as_longlong(vf) != __double_as_longlong(vi)) ||
+                          (__double_as_longlong(uf) != __double_as_longlong(ui));
+            } else {
+                const double vo = __ldcg(A.vn + s), uo = __ldcg(A.un + s);
+                changed = (__double_as_longlong(vf) != __double_as_longlong(vo)) ||
+                          (__double_as_longlong(uf) != __double_as_longlong(uo));
+                // a, du feed the next step's first kick: they must come from THIS (possibly final)
+                // evaluation even when the kicked values round to what is already stored
+                A.a[s] = a_sum; A.du[s] = e_sum;
+                if (changed) { __stcg(A.vn + s, vf); __stcg(A.un + s, uf); }
+            }
+            if (changed && SEL == SEL_INDEX) {
+                // every tile holding a particle within reach must be looked at again next sweep
+                const int ntiles = (A.na + kTile - 1) / kTile;
+                int ta = max((jmin - A.pad) / kTile, 0), tb = min((jmax - A.pad) / kTile, ntiles - 1);
+                if (jmin < A.pad) ta = 0;
+                for (int t = ta; t <= tb; t++) {
+                    if (atomicMax(A.dirty + t, epoch) < epoch) {
+                        const int slot = atomicAdd(&A.ctl->nwork[(epoch + 1) % 3], 1);
+                        A.wl[(epoch + 1) % 3][slot] = t;
+                    }
+                }
+            }
+        }
+    }
+    changed_any = changed;
+    npairs_out = npairs;
+}
+
+// First force sweep of a step over every alive particle (also the only one for the
+// jacobi order and for the kick-less t = 0 pass).
+template <int SEL, bool ADIA, bool UM>
+__global__ void __launch_bounds__(kTile, 4) k_force_first(SweepArgs A) {
+    Ctl *ctl = A.ctl;
+    const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
+    const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
+    bool changed;
+    int npairs;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->epoch_cur = A.epoch; ctl->sweeps_used = 1; }
+    force_tile<SEL, ADIA, UM, true>(A, blockIdx.x, lo, hi, Hb, A.epoch, changed, npairs);
+    // pair statistics for the roofline accounting (one atomic per warp)
+    for (int o = 16; o > 0; o >>= 1) npairs += __shfl_xor_sync(0xffffffffu, npairs, o);
+    if ((threadIdx.x & 31) == 0 && npairs) atomicAdd(&ctl->force_pairs, (unsigned long long)npairs);
+}
+
+// Refinement of the ordered sweep: ONE persistent cooperative launch that repeats
+// "recompute every tile in range of a particle whose kicked (v,u) changed in the
+// previous sweep" until a whole sweep changes nothing.  The dependency of particle i on
+// the fully-kicked (v,u) of its lower-index neighbours is strictly lower triangular, so
+// this fixed point exists, is unique, is reached after finitely many sweeps and IS the
+// result of the reference's sequential in-place sweep.
+// A sweep works through the work list its predecessor filled (tiles are appended once per
+// sweep, guarded by the atomicMax on their stamp); a sweep that appends nothing proves
+// that every particle was last computed from the final values.
+template <bool ADIA, bool UM>
+__global__ void __launch_bounds__(kTile) k_force_refine(SweepArgs A, int max_sweeps) {
+    cg::grid_group grid = cg::this_grid();
+    Ctl *ctl = A.ctl;
+    const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
+    const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
+    int epoch = ctl->epoch_cur;   // stamp of the latest sweep, which filled wl[(epoch + 1) % 3]
+    int used = ctl->sweeps_used;
+    int peak = 0;
+    grid.sync();                  // everybody has read the hand-over words before block 0 rewrites them
+    // Three rotating lists make ONE grid-wide barrier per sweep enough: sweep e reads list e % 3, fills
+    // (e + 1) % 3 and clears (e + 2) % 3, which every CTA finished reading before the previous barrier.
+    while (true) {
+        const int cur = (epoch + 1) % 3;
+        const int nwork = *((volatile int *)&ctl->nwork[cur]);
+        if (nwork == 0) break;
+        if (used >= max_sweeps) {
+            if (blockIdx.x == 0 && threadIdx.x == 0) raise(ctl, E_NOT_CONVERGED, -1);
+            break;
+        }
+        epoch++;
+        used++;
+        peak = max(peak, nwork);
+        if (blockIdx.x == 0 && threadIdx.x == 0) ctl->nwork[(epoch + 2) % 3] = 0;
+        for (int w = blockIdx.x; w < nwork; w += gridDim.x) {
+            const int tile = __ldcg(A.wl[cur] + w);
+            bool changed;
+            int npairs;
+            force_tile<SEL_INDEX, ADIA, UM, false>(A, tile, lo, hi, Hb, epoch, changed, npairs);
+        }
+        grid.sync();
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && peak > ctl->nwork_peak) ctl->nwork_peak = peak;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->sweeps_used = used; ctl->epoch_cur = epoch; }
+}
+
+// ------------------------------------------------------------------------------------
+// First half of the step (sph_simulation.cpp:59-73): v += a dt/2; u += du dt/2;
+// x += v dt, each product and sum rounded as written.  Fused with it: the ghost
+// predicate of ghost_particles.cpp:45-55 (stream compaction by atomic append: only the
+// handful of particles next to a wall ever qualify) and the x-order check.
+struct KickArgs {
+    const double *x;   // positions before the drift
+    double *xo;        // positions after the drift (a different buffer: the order check re-derives
+                       // the left neighbour's new position from the OLD arrays, race-free)
+    const double *v, *u, *a, *du, *h;
+    double *vh, *uh;
+    int *cand;
+    Ctl *ctl;
+    int pad, na, cand_cap;
+    double dt, half_dt, limit;
+    int do_kick;      // 0: ghost selection + order check only (positions unchanged, xo unused)
+};
+
+__device__ __forceinline__ bool ghost_predicate(double pos, double h, double limit) {
+    const double reach = __dmul_rn(kRadius, h);
+    const double max_pos = __dsub_rn(limit, reach);
+    const double min_pos = __dadd_rn(-limit, reach);
+    return pos > max_pos || pos < min_pos;
+}
+
+__global__ void __launch_bounds__(kTile) k_kick_drift(KickArgs A) {
+    __shared__ double sx[kTile + 1];
+    const int g = blockIdx.x * kTile + threadIdx.x;
+    const int s = A.pad + g;
+    double xn = 0.0;
+    if (g < A.na) {
+        if (A.do_kick) {
+            const double vhalf = __dadd_rn(A.v[s], __dmul_rn(A.a[s], A.half_dt));
+            const double uhalf = __dadd_rn(A.u[s], __dmul_rn(A.du[s], A.half_dt));
+            xn = __dadd_rn(A.x[s], __dmul_rn(vhalf, A.dt));
+            A.vh[s] = vhalf;
+            A.uh[s] = uhalf;
+            A.xo[s] = xn;
+        } else {
+            xn = A.x[s];
+        }
+        const double hh = A.h[s];
+        if (hh < kEps) raise(A.ctl, E_GHOST_ZERO_H, s);
+        if (ghost_predicate(xn, hh, A.limit)) {
+            int k = atomicAdd(&A.ctl->ncand, 1);
+            if (k < A.cand_cap) A.cand[k] = s;
+        }
+        sx[threadIdx.x + 1] = xn;
+    }
+    if (threadIdx.x == 0) {
+        double xp = -INFINITY;
+        if (g > 0 && g < A.na) {
+            if (A.do_kick) {
+                const double vp = __dadd_rn(A.v[s - 1], __dmul_rn(A.a[s - 1], A.half_dt));
+                xp = __dadd_rn(A.x[s - 1], __dmul_rn(vp, A.dt));
+            } else xp = A.x[s - 1];
+        }
+        sx[0] = xp;
+    }
+    __syncthreads();
+    if (g < A.na && sx[threadIdx.x] > xn) A.ctl->unsorted = 1;
+}
+
+__global__ void __launch_bounds__(kTile) k_check_sorted(const double *x, Ctl *ctl, int pad, int na) {
+    const int g = blockIdx.x * kTile + threadIdx.x;
+    if (g > 0 && g < na && x[pad + g - 1] > x[pad + g]) ctl->unsorted = 1;
+}
+
+// ------------------------------------------------------------------------------------
+// Ghost set-up (ghost_particles.cpp:57-115) for the selected candidates: mirrored
+// position, negated velocity, everything else copied; placed x-sorted into the pads and
+// remembered in ascending source-index order for the download (the reference appends
+// them in alive-index order).  One CTA: the candidate count is O(10) at any N.
+struct GhostArgs {
+    double *x, *vd, *ud, *a, *du, *h, *rho, *P, *m;   // vd/ud: the v,u arrays the ghosts live in
+    double *ad, *dud;                                  // the acc, du_dt arrays the ghosts live in (a, du: sources)
+    const double *vs, *us;                             // the v,u arrays the sources are read from
+    unsigned *idx;
+    const int *cand;
+    // staging (capacity 2*pad each)
+    double *gx, *gv, *gu, *ga, *gdu, *gh, *grho, *gP, *gm;
+    unsigned *gkey;
+    int *gorder;       // download order k -> pad slot
+    Ctl *ctl;
+    int pad, na, cand_cap;
+    double limit;
+    int from_alive;    // 1: stage from the alive candidates; 0: staging already filled (upload)
+    int nstaged;       // number staged when from_alive = 0
+};
+
+__global__ void __launch_bounds__(1024) k_ghost_build(GhostArgs G) {
+    Ctl *ctl = G.ctl;
+    __shared__ int s_nl;
+    int nc = G.from_alive ? ctl->ncand : G.nstaged;
+    if (nc > G.cand_cap) {
+        if (threadIdx.x == 0) { raise(ctl, E_CAPACITY, -1); ctl->GL = 0; ctl->GR = 0; }
+        return;
+    }
+    if (G.from_alive) {
+        for (int c = threadIdx.x; c < nc; c += blockDim.x) {
+            const int s = G.cand[c];
+            const double p = G.x[s];
+            // ghost_particles.cpp:60-69: the side is chosen by the sign of x
+            const double vec = (p < 0) ? __dsub_rn(-G.limit, p) : __dsub_rn(G.limit, p);
+            G.gx[c] = __dadd_rn(p, __dmul_rn(2.0, vec));
+            G.gv[c] = -G.vs[s];
+            G.gu[c] = G.us[s];
+            G.ga[c] = G.a[s];
+            G.gdu[c] = G.du[s];
+            G.gh[c] = G.h[s];
+            G.grho[c] = G.rho[s];
+            G.gP[c] = G.P[s];
+            G.gm[c] = G.m[s];
+            G.gkey[c] = G.idx[s];
+        }
+    }
+    if (threadIdx.x == 0) s_nl = 0;
+    __syncthreads();
+    int nl_local = 0;
+    for (int c = threadIdx.x; c < nc; c += blockDim.x) nl_local += (G.gx[c] < 0) ? 1 : 0;
+    if (nl_local) atomicAdd(&s_nl, nl_local);
+    __syncthreads();
+    const int GL = s_nl, GR = nc - GL;
+    if (GL > G.pad || GR > G.pad) {
+        if (threadIdx.x == 0) { raise(ctl, E_CAPACITY, -1); ctl->GL = 0; ctl->GR = 0; }
+        return;
+    }
+    for (int c = threadIdx.x; c < nc; c += blockDim.x) {
+        const double xc = G.gx[c];
+        const bool left = xc < 0;
+        const unsigned kc = G.gkey[c];
+        int rank_x = 0, rank_k = 0;
+        for (int d = 0; d < nc; d++) {
+            const double xd = G.gx[d];
+            if ((xd < 0) == left && (xd < xc || (xd == xc && d < c))) rank_x++;
+            const unsigned kd = G.gkey[d];
+            if (kd < kc || (kd == kc && d < c)) rank_k++;
+        }
+        const int dest = left ? (G.pad - GL + rank_x) : (G.pad + G.na + rank_x);
+        G.x[dest] = xc;
+        G.vd[dest] = G.gv[c];
+        G.ud[dest] = G.gu[c];
+        G.ad[dest] = G.ga[c];
+        G.dud[dest] = G.gdu[c];
+        G.h[dest] = G.gh[c];
+        G.rho[dest] = G.grho[c];
+        G.P[dest] = G.gP[c];
+        G.m[dest] = G.gm[c];
+        G.idx[dest] = kGhostBit | kc;
+        G.gorder[rank_k] = dest;
+    }
+    if (threadIdx.x == 0) { ctl->GL = GL; ctl->GR = GR; }
+}
+
+// copy ghost (pad) entries of v,u between the half-kicked and the current arrays
+__global__ void k_copy_pads(const double *vs, const double *us, double *vd, double *ud, const Ctl *ctl,
+                            int pad, int na) {
+    const int GL = ctl->GL, GR = ctl->GR;
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < GL + GR; k += gridDim.x * blockDim.x) {
+        const int s = k < GL ? (pad - GL + k) : (pad + na + (k - GL));
+        vd[s] = vs[s];
+        ud[s] = us[s];
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// AoS (the reference's Particle, 88 bytes) <-> SoA.
+struct AosRec {
+    int id, pad0;
+    double mass, pos, vel, acc, h, du_dt, u, density, pressure;
+    int type, pad1;
+};
+static_assert(sizeof(AosRec) == 88, "Particle layout");
+
+struct PackArgs {
+    double *x, *v, *u, *a, *du, *h, *rho, *P, *m;
+    unsigned *idx;
+    int *slot_id;
+    double *gx, *gv, *gu, *ga, *gdu, *gh, *grho, *gP, *gm;
+    unsigned *gkey;
+    const double *vg, *ug;     // arrays holding the ghosts' v,u at download time
+    const int *gorder;
+    const int *cnt;
+    AosRec *aos;
+    int *out_newton, *out_nbr;
+    const Ctl *ctl;
+    int pad, na, ng;
+    unsigned idx_base;   // global index of the first local particle (x-slabs), else 0
+};
+
+__global__ void k_unpack(PackArgs A) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= A.na + A.ng) return;
+    const AosRec r = A.aos[i];
+    A.slot_id[i] = r.id;
+    if (i < A.na) {
+        const int s = A.pad + i;
+        A.x[s] = r.pos; A.v[s] = r.vel; A.u[s] = r.u; A.a[s] = r.acc; A.du[s] = r.du_dt;
+        A.h[s] = r.h; A.rho[s] = r.density; A.P[s] = r.pressure; A.m[s] = r.mass;
+        A.idx[s] = (unsigned)i + A.idx_base;
+    } else {
+        const int k = i - A.na;
+        A.gx[k] = r.pos; A.gv[k] = r.vel; A.gu[k] = r.u; A.ga[k] = r.acc; A.gdu[k] = r.du_dt;
+        A.gh[k] = r.h; A.grho[k] = r.density; A.gP[k] = r.pressure; A.gm[k] = r.mass;
+        A.gkey[k] = (unsigned)k;
+    }
+}
+
+__global__ void k_pack(PackArgs A) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int ng = A.ng;
+    if (t >= A.na + ng) return;
+    int s, out;
+    const double *vv, *uu;
+    int type;
+    if (t < A.na) {
+        s = A.pad + t;
+        out = (int)(A.idx[s] - A.idx_base);
+        vv = A.v; uu = A.u; type = 0;
+    } else {
+        s = A.gorder[t - A.na];
+        out = t;
+        vv = A.vg; uu = A.ug; type = 1;
+    }
+    AosRec r;
+    r.id = A.slot_id[out]; r.pad0 = 0;
+    r.mass = A.m[s]; r.pos = A.x[s]; r.vel = vv[s]; r.acc = A.a[s]; r.h = A.h[s];
+    r.du_dt = A.du[s]; r.u = uu[s]; r.density = A.rho[s]; r.pressure = A.P[s];
+    r.type = type; r.pad1 = 0;
+    A.aos[out] = r;
+    if (A.out_newton) {
+        const int c = A.cnt[s];
+        A.out_newton[out] = (c >> 24) & 0xff;
+        A.out_nbr[out] = c & 0xffffff;
+    }
+}
+
+// one double per particle, sorted slot -> array-index order (same mapping as k_pack)
+__global__ void k_pack_f64(const double *src, double *out, const unsigned *idx, const int *gorder, const Ctl *ctl,
+                           int pad, int na, int ng, unsigned idx_base) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= na + ng) return;
+    if (t < na) {
+        const int s = pad + t;
+        out[idx[s] - idx_base] = src[s];
+    } else {
+        out[t] = src[gorder[t - na]];
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// x-slab decomposition: the K particles next to a slab edge travel to the
+// neighbouring rank and fill ITS pad on the facing side, in the same ascending-x order, so that
+// every kernel above runs unchanged.  Messages are rows of K doubles plus a header row.
+//   BASE    after the drift:  x, m, v_half, u_half, h_old, rho_old, P, idx            (8 rows)
+//   RECORDS after the density pass: the owner's Rec2                                   (8 rows)
+//   ITERATE during the ordered sweep: current fully kicked v, u                        (2 rows)
+// header[0] = number of particles in the message.
+enum { MSG_BASE = 0, MSG_RECORDS = 1, MSG_ITERATE = 2 };
+__host__ __device__ inline int msg_rows(int what) { return what == MSG_ITERATE ? 2 : 8; }
+
+struct SlabArgs {
+    double *x, *m, *vh, *uh, *vn, *un, *h, *rho, *P;
+    unsigned *idx;
+    Rec2 *rec;
+    int *dirty;
+    int *wl[3];
+    Ctl *ctl;
+    int pad, na, K;
+    int side;        // -1: my left edge / my left pad, +1: right
+};
+
+// my edge particles -> message (side = which of my edges)
+__global__ void k_slab_pack(SlabArgs A, int what, double *buf) {
+    const int cnt = min(A.K, A.na);
+    const int first = A.side < 0 ? A.pad : A.pad + A.na - cnt;
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < cnt; k += gridDim.x * blockDim.x) {
+        const int s = first + k;
+        if (what == MSG_BASE) {
+            buf[0 * A.K + k] = A.x[s]; buf[1 * A.K + k] = A.m[s]; buf[2 * A.K + k] = A.vh[s];
+            buf[3 * A.K + k] = A.uh[s]; buf[4 * A.K + k] = A.h[s]; buf[5 * A.K + k] = A.rho[s];
+            buf[6 * A.K + k] = A.P[s]; buf[7 * A.K + k] = (double)A.idx[s];
+        } else if (what == MSG_RECORDS) {
+            const Rec2 r = A.rec[s];
+            buf[0 * A.K + k] = r.A.h; buf[1 * A.K + k] = r.A.c5; buf[2 * A.K + k] = r.A.rho; buf[3 * A.K + k] = r.A.kap;
+            buf[4 * A.K + k] = r.B.h; buf[5 * A.K + k] = r.B.c5; buf[6 * A.K + k] = r.B.rho; buf[7 * A.K + k] = r.B.kap;
+        } else {
+            buf[0 * A.K + k] = A.vn[s]; buf[1 * A.K + k] = A.un[s];
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        buf[msg_rows(what) * A.K] = (double)cnt;
+        if (what == MSG_ITERATE) A.ctl->halo_changed = 0;   // the unpack that follows this exchange sets it again
+    }
+}
+
+// message from the neighbour on `side` -> my pad on that side.  One CTA.
+__global__ void __launch_bounds__(1024) k_slab_unpack(SlabArgs A, int what, const double *buf) {
+    Ctl *ctl = A.ctl;
+    const int cnt = (int)buf[msg_rows(what) * A.K];
+    if (cnt < 0 || cnt > A.K || cnt > A.pad) {
+        if (threadIdx.x == 0) raise(ctl, E_CAPACITY, -1);
+        return;
+    }
+    // a message from my LEFT neighbour holds ITS last particles: they end right before my first one
+    const int first = A.side < 0 ? A.pad - cnt : A.pad + A.na;
+    __shared__ int s_changed, s_tile;
+    if (threadIdx.x == 0) { s_changed = 0; s_tile = A.side < 0 ? -1 : 0x7fffffff; }
+    __syncthreads();
+    const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
+    const int ntiles = (A.na + kTile - 1) / kTile;
+    for (int k = threadIdx.x; k < cnt; k += blockDim.x) {
+        const int s = first + k;
+        if (what == MSG_BASE) {
+            A.x[s] = buf[0 * A.K + k]; A.m[s] = buf[1 * A.K + k];
+            const double v = buf[2 * A.K + k], u = buf[3 * A.K + k];
+            A.vh[s] = v; A.uh[s] = u;
+            A.vn[s] = v; A.un[s] = u;            // first guess of the neighbour's fully kicked values
+            A.h[s] = buf[4 * A.K + k]; A.rho[s] = buf[5 * A.K + k]; A.P[s] = buf[6 * A.K + k];
+            A.idx[s] = (unsigned)buf[7 * A.K + k];
+        } else if (what == MSG_RECORDS) {
+            Rec2 r;
+            r.A.h = buf[0 * A.K + k]; r.A.c5 = buf[1 * A.K + k]; r.A.rho = buf[2 * A.K + k]; r.A.kap = buf[3 * A.K + k];
+            r.B.h = buf[4 * A.K + k]; r.B.c5 = buf[5 * A.K + k]; r.B.rho = buf[6 * A.K + k]; r.B.kap = buf[7 * A.K + k];
+            A.rec[s] = r;
+            // the scan bound of the force pass must cover the neighbour's smoothing lengths too
+            atomicMax(&ctl->hmax_bits, (unsigned long long)__double_as_longlong(fmax(r.A.h, r.B.h)));
+        } else {
+            const double v = buf[0 * A.K + k], u = buf[1 * A.K + k];
+            if (__double_as_longlong(v) != __double_as_longlong(A.vn[s]) ||
+                __double_as_longlong(u) != __double_as_longlong(A.un[s])) {
+                A.vn[s] = v; A.un[s] = u;
+                // Only particles that see this neighbour in its NEW state depend on the value: own
+                // particles within reach whose array index is higher (the sweep reaches them later).
+                // Without one, the new value is merely kept.
+                const double xj = A.x[s];
+                const unsigned idxj = A.idx[s];
+                bool relevant = false;
+                if (A.side < 0) {
+                    int q = A.pad;
+                    while (q < A.pad + A.na && A.x[q] - xj < kRadius * Hb) { relevant |= A.idx[q] > idxj; q++; }
+                    if (relevant) atomicMax(&s_tile, (q - 1 - A.pad) / kTile);
+                } else {
+                    int q = A.pad + A.na - 1;
+                    while (q >= A.pad && xj - A.x[q] < kRadius * Hb) { relevant |= A.idx[q] > idxj; q--; }
+                    if (relevant) atomicMin(&s_tile, (q + 1 - A.pad) / kTile);
+                }
+                if (relevant) s_changed = 1;
+            }
+        }
+    }
+    __syncthreads();
+    if (what == MSG_BASE && threadIdx.x == 0) {
+        if (A.side < 0) { ctl->GL = cnt; ctl->halo_left = 1; } else { ctl->GR = cnt; ctl->halo_right = 1; }
+        // the slabs must stay ordered across the edge too: a particle that overtook its neighbour on
+        // the other rank has to migrate (sphb_slab_* callers rebalance when they see this code)
+        if (cnt > 0 && A.na > 0) {
+            const bool bad = A.side < 0 ? (A.x[A.pad - 1] > A.x[A.pad]) : (A.x[A.pad + A.na - 1] > A.x[A.pad + A.na]);
+            if (bad) raise(ctl, E_UNSORTED, A.side < 0 ? A.pad : A.pad + A.na - 1);
+        }
+    }
+    if (what == MSG_ITERATE && s_changed) {
+        // queue those tiles for the next sweep, exactly like a changed particle of my own would
+        const int epoch = ctl->epoch_cur;
+        const int ta = A.side < 0 ? 0 : min(s_tile, ntiles);
+        const int tb = A.side < 0 ? min(s_tile, ntiles - 1) : ntiles - 1;
+        for (int t = ta + threadIdx.x; t <= tb; t += blockDim.x) {
+            if (atomicMax(A.dirty + t, epoch) < epoch) {
+                const int slot = atomicAdd(&ctl->nwork[(epoch + 1) % 3], 1);
+                A.wl[(epoch + 1) % 3][slot] = t;
+            }
+        }
+        if (threadIdx.x == 0) ctl->halo_changed = 1;
+    }
+}
+
+__global__ void k_slab_flags(Ctl *ctl, int hl, int hr) { ctl->halo_left = hl; ctl->halo_right = hr; }
+
+// ------------------------------------------------------------------------------------
+// sort support
+__global__ void k_iota(int *p, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = i;
+}
+__global__ void k_gather_f64(const double *in, double *out, const int *perm, int pad, int na) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < na) out[pad + i] = in[pad + perm[i]];
+}
+__global__ void k_gather_u32(const unsigned *in, unsigned *out, const int *perm, int pad, int na) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < na) out[pad + i] = in[pad + perm[i]];
+}
+
+// ------------------------------------------------------------------------------------
+// t = 0 lattice (setup.cpp:145-185) and the adiabatic pre-pass's pressure / +-c_s
+// velocities (setup.cpp:197-201).
+struct LatticeArgs {
+    double *x, *v, *u, *a, *du, *h, *rho, *P, *m;
+    unsigned *idx;
+    int *slot_id;
+    int pad, na;
+    long long i0;      // global index of this handle's first particle (x-slabs)
+    double min_x, spacing, v0, u0, h0, mass;
+};
+__global__ void k_lattice(LatticeArgs A) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= A.na) return;
+    const int s = A.pad + i;
+    const double pos = __dadd_rn(A.min_x, __dmul_rn(A.spacing, (double)(A.i0 + i)));
+    A.x[s] = pos;
+    A.v[s] = (pos < 0) ? A.v0 : -A.v0;
+    A.u[s] = A.u0;
+    A.h[s] = A.h0;
+    A.m[s] = A.mass;
+    A.a[s] = 0; A.du[s] = 0; A.rho[s] = 0; A.P[s] = 0;
+    A.idx[s] = (unsigned)(A.i0 + i);
+    A.slot_id[i] = (int)(A.i0 + i);
+}
+__global__ void k_prepass(const double *x, double *v, const double *u, const double *rho, double *P, int pad,
+                          int na) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= na) return;
+    const int s = pad + i;
+    const double Pi = ((kGamma - 1) * u[s]) * rho[s];
+    P[s] = Pi;
+    const double c = sqrt(kGamma * Pi / rho[s]);
+    v[s] = (x[s] < 0) ? c : -c;
+}
+
+__global__ void k_begin(Ctl *ctl, int clear_cand) {
+    ctl->hmax_bits = 0ull;
+    ctl->unsorted = 0;
+    if (clear_cand) ctl->ncand = 0;
+    ctl->nwork[0] = 0;
+    ctl->nwork[1] = 0;
+    ctl->nwork[2] = 0;
+    ctl->nwork_peak = 0;
+    ctl->halo_changed = 0;
+    ctl->force_pairs = 0ull;
+}
+
+}  // namespace sphb
