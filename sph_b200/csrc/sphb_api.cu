@@ -264,16 +264,16 @@ int launch_density(sphb_handle *H, int root_alive, int root_ghosts, int check_ol
     A.cnt = H->cnt; A.ctl = H->d_ctl; A.pad = H->pad; A.na = H->na;
     A.limit = H->cfg.limit; A.hfac = H->cfg.h_factor; A.m0 = H->m0;
     A.root_ghosts = root_ghosts; A.root_alive = root_alive; A.check_old = check_old;
-    int grid = nblk(H->na + 2 * H->pad, kTile);
-    A.tile_split = grid; A.tile_skip = 0;
+    const int ntot = nblk(H->na + 2 * H->pad, kTile);
+    // tile ranges [begin, end) to launch: everything, or (x-slab overlap) the interior / the two edges;
+    // edge = every tile that can see a pad: the pads themselves plus K + one tile of own particles
+    int ranges[2][2] = {{0, ntot}, {0, 0}};
     if (H->part) {
-        // edge = every tile that can see a pad: the pads themselves plus K + one tile of own particles
         const int e = H->K + kTile;
-        const int tl = std::min(grid, nblk(H->pad + e, kTile));
+        const int tl = std::min(ntot, nblk(H->pad + e, kTile));
         const int tr = std::max(tl, (H->pad + H->na - e) / kTile);
-        if (H->part == 1) { A.tile_split = 0; A.tile_skip = tl; grid = tr - tl; }
-        else { A.tile_split = tl; A.tile_skip = tr - tl; grid = grid - (tr - tl); }
-        if (grid <= 0) return SPHB_OK;
+        if (H->part == 1) { ranges[0][0] = tl; ranges[0][1] = tr; }
+        else { ranges[0][0] = 0; ranges[0][1] = tl; ranges[1][0] = tr; ranges[1][1] = ntot; }
     }
     const bool varh = H->opt.variable_h != 0;
 #define SPHB_DENS(V, U)                                                              \
@@ -281,27 +281,31 @@ int launch_density(sphb_handle *H, int root_alive, int root_ghosts, int check_ol
         if (H->slab) k_density<V, U, true><<<grid, kTile, 0, H->stream>>>(A);        \
         else k_density<V, U, false><<<grid, kTile, 0, H->stream>>>(A);               \
     } while (0)
-    if (varh && H->uniform_mass) SPHB_DENS(true, true);
-    else if (varh) SPHB_DENS(true, false);
-    else if (H->uniform_mass) SPHB_DENS(false, true);
-    else SPHB_DENS(false, false);
+    for (auto &rg : ranges) {
+        const int grid = rg[1] - rg[0];
+        if (grid <= 0) continue;
+        A.tile_base = rg[0];
+        if (varh && H->uniform_mass) SPHB_DENS(true, true);
+        else if (varh) SPHB_DENS(true, false);
+        else if (H->uniform_mass) SPHB_DENS(false, true);
+        else SPHB_DENS(false, false);
+        H->launches++;
+        CK(cudaGetLastError());
+    }
 #undef SPHB_DENS
-    H->launches++;
-    CK(cudaGetLastError());
     if (root_alive || root_ghosts) H->have_counts = true;
     return SPHB_OK;
 }
 
 template <int SEL>
 int launch_first_sel(sphb_handle *H, SweepArgs A) {
-    int grid = nblk(H->na, kTile);
-    A.tile_split = grid; A.tile_skip = 0;
+    const int ntiles = nblk(H->na, kTile);
+    int ranges[2][2] = {{0, ntiles}, {0, 0}};
     if (H->part) {
-        const int te = std::min(grid, nblk(H->K + kTile, kTile));
-        const int tr = std::max(te, grid - te);
-        if (H->part == 1) { A.tile_split = 0; A.tile_skip = te; grid = tr - te; }
-        else { A.tile_split = te; A.tile_skip = tr - te; grid = grid - (tr - te); }
-        if (grid <= 0) return SPHB_OK;
+        const int te = std::min(ntiles, nblk(H->K + kTile, kTile));
+        const int tr = std::max(te, ntiles - te);
+        if (H->part == 1) { ranges[0][0] = te; ranges[0][1] = tr; }
+        else { ranges[0][0] = 0; ranges[0][1] = te; ranges[1][0] = tr; ranges[1][1] = ntiles; }
     }
     const bool adia = H->cfg.pressure_calc == SPHB_ADIABATIC;
 #define SPHB_FIRST(AD, U)                                                                        \
@@ -309,13 +313,18 @@ int launch_first_sel(sphb_handle *H, SweepArgs A) {
         if (H->part) k_force_first<SEL, AD, U, true><<<grid, kTile, 0, H->stream>>>(A);          \
         else k_force_first<SEL, AD, U, false><<<grid, kTile, 0, H->stream>>>(A);                 \
     } while (0)
-    if (adia && H->uniform_mass) SPHB_FIRST(true, true);
-    else if (adia) SPHB_FIRST(true, false);
-    else if (H->uniform_mass) SPHB_FIRST(false, true);
-    else SPHB_FIRST(false, false);
+    for (auto &rg : ranges) {
+        const int grid = rg[1] - rg[0];
+        if (grid <= 0) continue;
+        A.tile_base = rg[0];
+        if (adia && H->uniform_mass) SPHB_FIRST(true, true);
+        else if (adia) SPHB_FIRST(true, false);
+        else if (H->uniform_mass) SPHB_FIRST(false, true);
+        else SPHB_FIRST(false, false);
+        H->launches++;
+        CK(cudaGetLastError());
+    }
 #undef SPHB_FIRST
-    H->launches++;
-    CK(cudaGetLastError());
     return SPHB_OK;
 }
 
@@ -1382,7 +1391,7 @@ int sphb_density_static(const double *d_x, const double *d_h, const double *d_rh
     A.limit = limit; A.hfac = h_factor; A.m0 = mass;
     A.root_ghosts = 0; A.root_alive = 1; A.check_old = 0;
     const int grid = nblk(n, kTile);
-    A.tile_split = grid; A.tile_skip = 0;
+    A.tile_base = 0;
     if (variable_h) k_density<true, true, false><<<grid, kTile, 0, st>>>(A);
     else k_density<false, true, false><<<grid, kTile, 0, st>>>(A);
     CK(cudaGetLastError());

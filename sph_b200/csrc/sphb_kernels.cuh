@@ -225,7 +225,7 @@ struct DensityArgs {
     int root_ghosts;     // 1: ghosts are root-found too (t = 0, setup.cpp:218-220)
     int root_alive;      // 0: omega-only pass (keeps h, rho; used by sphb_forces / sphb_omega)
     int check_old;       // 1: the old (h, rho) state is also seen by force sums (step path)
-    int tile_split, tile_skip;   // launch covers tiles b < split ? b : b + skip  (interior / edge launches of a slab)
+    int tile_base;       // the launch covers tiles tile_base + blockIdx.x (interior / edge launches of a slab)
 };
 
 // Fused density + variable-h root-find + omega, one thread per
@@ -243,8 +243,7 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
     double *sx = sxs + 1;
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
-    const int t0 = (!SLAB ? (int)blockIdx.x
-                          : ((int)blockIdx.x < A.tile_split ? (int)blockIdx.x : (int)blockIdx.x + A.tile_skip)) * kTile;   // tiles of [0, pad + na + pad)
+    const int t0 = (SLAB ? (int)blockIdx.x + A.tile_base : (int)blockIdx.x) * kTile;   // tiles of [0, pad + na + pad)
     if (t0 >= hi || t0 + kTile <= lo) return;
     const int wbase = max(t0 - kDHalo, lo);
     const int wn = min(t0 + kTile + kDHalo, hi) - wbase;
@@ -423,7 +422,7 @@ struct SweepArgs {
     int epoch;              // stamp of this sweep
     int kick;               // 0: t = 0 semantics (no kick, calculators only)
     double tol;             // 0: iterate to the bitwise fixed point; > 0: until every change is below tol (relative)
-    int tile_split, tile_skip;   // first sweep: launch covers tiles b < split ? b : b + skip
+    int tile_base;          // first sweep: the launch covers tiles tile_base + blockIdx.x
 };
 
 // per-thread invariants of one force evaluation
@@ -716,8 +715,7 @@ __global__ void __launch_bounds__(kTile, 4) k_force_first(SweepArgs A) {
     bool changed;
     int npairs;
     if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->epoch_cur = A.epoch; ctl->sweeps_used = 1; }
-    const int tile = !MAPPED ? (int)blockIdx.x
-                             : ((int)blockIdx.x < A.tile_split ? (int)blockIdx.x : (int)blockIdx.x + A.tile_skip);
+    const int tile = MAPPED ? (int)blockIdx.x + A.tile_base : (int)blockIdx.x;
     force_tile<SEL, ADIA, UM, true>(A, tile, lo, hi, Hb, A.epoch, changed, npairs);
     // pair statistics for the roofline accounting (one atomic per warp)
     for (int o = 16; o > 0; o >>= 1) npairs += __shfl_xor_sync(0xffffffffu, npairs, o);
