@@ -834,17 +834,18 @@ int sphb_upload(sphb_handle *H, const sphb_particle *aos, int n_part, int n_ghos
     CK(cudaSetDevice(H->device));
     TRY(ensure_aos(H, (size_t)n_part));
     CK(cudaMemcpyAsync(H->d_aos, aos, sizeof(AosRec) * (size_t)n_part, cudaMemcpyHostToDevice, H->stream));
-    // uniform masses let every kernel take m from a register instead of a per-neighbour load
-    bool uniform = true;
+    // uniform masses let every kernel take m from a register instead of a per-neighbour load; whether
+    // they are is decided on the device while unpacking (a host loop over the records costs more than
+    // the transfer itself at 64 Mi particles)
     const double m0 = aos[0].mass;
-    for (int i = 1; i < n_part && uniform; i++) uniform = (aos[i].mass == m0);
-    H->uniform_mass = uniform;
     H->m0 = m0;
+    CK(cudaMemsetAsync(&H->d_ctl->mass_differs, 0, sizeof(int), H->stream));
     H->na = na;
     H->cfg.n_part = n_part;
     H->cfg.n_ghost = n_ghost;
     PackArgs A = pack_args(H);
     A.ng = n_ghost;
+    A.m_first = m0; A.ctl_rw = H->d_ctl;
     k_unpack<<<nblk(n_part, 256), 256, 0, H->stream>>>(A);
     H->launches++;
     CK(cudaGetLastError());
@@ -853,6 +854,7 @@ int sphb_upload(sphb_handle *H, const sphb_particle *aos, int n_part, int n_ghos
     H->launches++;
     CK(cudaGetLastError());
     TRY(read_ctl(H));
+    H->uniform_mass = H->h_ctl->mass_differs == 0;
     if (H->h_ctl->unsorted) TRY(sort_alive(H, true));
     TRY(launch_ghost_build(H, 0, n_ghost, H->v, H->u, H->v, H->u));
     H->ghost_in_half = false;

@@ -58,6 +58,7 @@ struct Ctl {
     int epoch_cur;                 // stamp of the most recent force sweep (handed from launch to launch)
     int halo_left, halo_right;     // the pad on that side holds another slab's particles, not wall ghosts
     int halo_changed;              // an incoming halo iterate differed from the copy held here
+    int mass_differs;              // upload: some particle's mass is not the first particle's (cleared by the upload)
     unsigned long long force_pairs; // (i,j) pairs evaluated by the first force sweep (self included)
 };
 
@@ -732,7 +733,7 @@ __global__ void __launch_bounds__(kTile, 4) k_force_first(SweepArgs A) {
 // sweep, guarded by the atomicMax on their stamp); a sweep that appends nothing proves
 // that every particle was last computed from the final values.
 template <bool ADIA, bool UM>
-__global__ void __launch_bounds__(kTile) k_force_refine(SweepArgs A, int max_sweeps) {
+__global__ void __launch_bounds__(kTile, 3) k_force_refine(SweepArgs A, int max_sweeps) {
     cg::grid_group grid = cg::this_grid();
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
@@ -955,6 +956,8 @@ struct PackArgs {
     const Ctl *ctl;
     int pad, na, ng;
     unsigned idx_base;   // global index of the first local particle (x-slabs), else 0
+    double m_first;      // upload: mass of record 0 (uniform masses are taken from a register by the kernels)
+    Ctl *ctl_rw;
 };
 
 __global__ void k_unpack(PackArgs A) {
@@ -962,6 +965,7 @@ __global__ void k_unpack(PackArgs A) {
     if (i >= A.na + A.ng) return;
     const AosRec r = A.aos[i];
     A.slot_id[i] = r.id;
+    if (r.mass != A.m_first) A.ctl_rw->mass_differs = 1;
     if (i < A.na) {
         const int s = A.pad + i;
         A.x[s] = r.pos; A.v[s] = r.vel; A.u[s] = r.u; A.a[s] = r.acc; A.du[s] = r.du_dt;

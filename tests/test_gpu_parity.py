@@ -262,6 +262,31 @@ def test_download_upload_round_trip_is_idempotent():
     b.close()
 
 
+def test_against_oracle_at_one_million():
+    """SURVEY.md §8(d) parity gate at N = 1M (BASELINE config sizes start here): the O(N k) oracle on the
+    same inputs, t = 0 and three steps; rho, h, v, u to 1e-10, ghost count, Newton iteration counts,
+    neighbour counts (bracketed at the support edge)."""
+    n = 1_000_000
+    kw = dict(n_part=n, mass=4.0 / (n - 1), pressure_calc=1, limit=2.0, v_0=1.0, h_factor=2.0,
+              t_i=0.005 * 100 / (n - 1), variable_h=True, constant_h=0.2)
+    o = _oracle(kw)
+    sim = _sim(kw)
+    sim.init_lattice()
+    for st in range(0, 4):
+        if st:
+            o.step(1)
+            sim.step(1)
+        if st in (0, 3):
+            f, typ, ng = sim.fields()
+            ref = o.fields()
+            assert ng == o.n_ghost
+            _compare(f, ref, n, True, "N=1M step %d" % st)
+    nw, nb = sim.counts()
+    assert np.array_equal(nw[:n], o.newton_iters()[:n])
+    assert_neighbour_counts(nb, o.neighbour_counts(), ref, n, "N=1M step 3")
+    sim.close()
+
+
 def test_large_n_properties():
     """N = 1M (BASELINE config-2 size), adiabatic variable h: properties that need no oracle.
     The lattice is mirror-symmetric and both streams are uniform away from the centre and
