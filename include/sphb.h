@@ -181,7 +181,11 @@ int sphb_get_phase_times(sphb_handle *h, double *ms, long long *launches, int re
 enum { SPHB_MSG_BASE = 0, SPHB_MSG_RECORDS = 1, SPHB_MSG_ITERATE = 2 };
 /* this handle holds global particle indices [index_offset, index_offset + n_alive) of n_global;
  * halo_count particles travel per edge (must exceed the kernel reach in particles; too thin a halo is
- * detected on the device and reported as SPHB_ERR_HALO) */
+ * detected on the device and reported as SPHB_ERR_HALO).  A particle that overtakes its neighbour across a
+ * slab edge changes owner (both ranks merge-split the 2 x halo_count particles around the edge; counts stay
+ * equal), so a slab's particles are no longer a contiguous index range: in an x-slab run sphb_upload /
+ * sphb_download move the records in x ORDER and `id` carries the particle's GLOBAL index (the caller sets
+ * it on upload and reads it on download); sphb_init_lattice-style set-up needs no upload. */
 int sphb_slab_configure(sphb_handle *h, int rank, int world, int halo_count, long long index_offset,
                         long long n_global);
 int sphb_slab_message_doubles(const sphb_handle *h, int what);

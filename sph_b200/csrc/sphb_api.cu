@@ -520,6 +520,8 @@ PackArgs pack_args(sphb_handle *H) {
     A.out_newton = nullptr; A.out_nbr = nullptr;
     A.ctl = H->d_ctl; A.pad = H->pad; A.na = H->na; A.ng = 0;
     A.idx_base = (unsigned)H->idx_base;
+    A.by_slot = H->slab ? 1 : 0;
+    A.m_first = 0.0; A.ctl_rw = H->d_ctl;
     return A;
 }
 
@@ -1000,7 +1002,7 @@ int sphb_omega(sphb_handle *H, double *omega, int cap) {
     const int n = H->na + wall_ghosts(H);
     if (n > cap) { H->err = "download buffer too small"; return SPHB_ERR_CAPACITY; }
     k_pack_f64<<<nblk(n, 256), 256, 0, H->stream>>>(H->omn, H->tmp, H->idx, H->gorder, H->d_ctl, H->pad, H->na,
-                                                    n - H->na, (unsigned)H->idx_base);
+                                                    n - H->na, (unsigned)H->idx_base, H->slab ? 1 : 0);
     H->launches++;
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(omega, H->tmp, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, H->stream));

@@ -58,6 +58,7 @@ struct Ctl {
     int epoch_cur;                 // stamp of the most recent force sweep (handed from launch to launch)
     int halo_left, halo_right;     // the pad on that side holds another slab's particles, not wall ghosts
     int halo_changed;              // an incoming halo iterate differed from the copy held here
+    int migrated;                  // particles that changed slab in the current attempt
     int mass_differs;              // upload: some particle's mass is not the first particle's (cleared by the upload)
     unsigned long long force_pairs; // (i,j) pairs evaluated by the first force sweep (self included)
 };
@@ -110,6 +111,7 @@ struct __align__(64) Rec2 { Rec A, B; };   // new state (as seen once the sweep 
 
 constexpr int kDHalo = 64;    // density pass: x staged on each side of a tile
 constexpr int kFHalo = 32;    // force pass: neighbour state staged on each side of a tile
+constexpr int kMergeMax = 1024;  // largest halo_count for which a cross-edge merge-split is done on the device
 constexpr int kLocalIters = 48;  // cap on the in-tile iterations of one refinement sweep
 
 // ------------------------------------------------------------------------------------
@@ -956,6 +958,7 @@ struct PackArgs {
     const Ctl *ctl;
     int pad, na, ng;
     unsigned idx_base;   // global index of the first local particle (x-slabs), else 0
+    int by_slot;         // x-slab runs: records travel in x order and carry their global index in `id`
     double m_first;      // upload: mass of record 0 (uniform masses are taken from a register by the kernels)
     Ctl *ctl_rw;
 };
@@ -970,7 +973,7 @@ __global__ void k_unpack(PackArgs A) {
         const int s = A.pad + i;
         A.x[s] = r.pos; A.v[s] = r.vel; A.u[s] = r.u; A.a[s] = r.acc; A.du[s] = r.du_dt;
         A.h[s] = r.h; A.rho[s] = r.density; A.P[s] = r.pressure; A.m[s] = r.mass;
-        A.idx[s] = (unsigned)i + A.idx_base;
+        A.idx[s] = A.by_slot ? (unsigned)r.id : (unsigned)i + A.idx_base;
     } else {
         const int k = i - A.na;
         A.gx[k] = r.pos; A.gv[k] = r.vel; A.gu[k] = r.u; A.ga[k] = r.acc; A.gdu[k] = r.du_dt;
@@ -988,7 +991,7 @@ __global__ void k_pack(PackArgs A) {
     int type;
     if (t < A.na) {
         s = A.pad + t;
-        out = (int)(A.idx[s] - A.idx_base);
+        out = A.by_slot ? t : (int)(A.idx[s] - A.idx_base);
         vv = A.v; uu = A.u; type = 0;
     } else {
         s = A.gorder[t - A.na];
@@ -996,7 +999,7 @@ __global__ void k_pack(PackArgs A) {
         vv = A.vg; uu = A.ug; type = 1;
     }
     AosRec r;
-    r.id = A.slot_id[out]; r.pad0 = 0;
+    r.id = (A.by_slot && t < A.na) ? (int)A.idx[s] : A.slot_id[out]; r.pad0 = 0;
     r.mass = A.m[s]; r.pos = A.x[s]; r.vel = vv[s]; r.acc = A.a[s]; r.h = A.h[s];
     r.du_dt = A.du[s]; r.u = uu[s]; r.density = A.rho[s]; r.pressure = A.P[s];
     r.type = type; r.pad1 = 0;
@@ -1010,12 +1013,12 @@ __global__ void k_pack(PackArgs A) {
 
 // one double per particle, sorted slot -> array-index order (same mapping as k_pack)
 __global__ void k_pack_f64(const double *src, double *out, const unsigned *idx, const int *gorder, const Ctl *ctl,
-                           int pad, int na, int ng, unsigned idx_base) {
+                           int pad, int na, int ng, unsigned idx_base, int by_slot) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= na + ng) return;
     if (t < na) {
         const int s = pad + t;
-        out[idx[s] - idx_base] = src[s];
+        out[by_slot ? t : (int)(idx[s] - idx_base)] = src[s];
     } else {
         out[t] = src[gorder[t - na]];
     }
@@ -1125,11 +1128,65 @@ __global__ void __launch_bounds__(1024) k_slab_unpack(SlabArgs A, int what, cons
     __syncthreads();
     if (what == MSG_BASE && threadIdx.x == 0) {
         if (A.side < 0) { ctl->GL = cnt; ctl->halo_left = 1; } else { ctl->GR = cnt; ctl->halo_right = 1; }
-        // the slabs must stay ordered across the edge too: a particle that overtook its neighbour on
-        // the other rank has to migrate (sphb_slab_* callers rebalance when they see this code)
-        if (cnt > 0 && A.na > 0) {
-            const bool bad = A.side < 0 ? (A.x[A.pad - 1] > A.x[A.pad]) : (A.x[A.pad + A.na - 1] > A.x[A.pad + A.na]);
-            if (bad) raise(ctl, E_UNSORTED, A.side < 0 ? A.pad : A.pad + A.na - 1);
+    }
+    if (what == MSG_BASE) {
+        // The slabs must stay ordered ACROSS the edge too.  When the drift made the last particle of the left
+        // slab overtake the first of the right one, both ranks hold the same 2K particles (their own edge and
+        // the message) and do the same merge-split on them: the lower ones stay / go left, the upper ones
+        // right, counts unchanged, no further message needed.  Everything a particle owns at this point of
+        // the step is in the BASE message.
+        __syncthreads();
+        const int ko = min(A.K, A.na);
+        const int lfirst = A.side < 0 ? A.pad - cnt : A.pad + A.na - ko;   // the left set of the 2K window
+        const int nleft = A.side < 0 ? cnt : ko, nright = A.side < 0 ? ko : cnt;
+        const int ntot = nleft + nright;
+        __shared__ int s_inv;
+        if (threadIdx.x == 0) {
+            const int a = lfirst + nleft - 1, b = lfirst + nleft;         // last of the left set, first of the right set
+            s_inv = (nleft > 0 && nright > 0 &&
+                     (A.x[a] > A.x[b] || (A.x[a] == A.x[b] && A.idx[a] > A.idx[b]))) ? 1 : 0;
+        }
+        __syncthreads();
+        if (s_inv) {
+            if (ntot > 2 * kMergeMax) { if (threadIdx.x == 0) raise(ctl, E_UNSORTED, lfirst); return; }
+            __shared__ double s_kx[2 * kMergeMax];
+            __shared__ unsigned s_ki[2 * kMergeMax];
+            for (int e = threadIdx.x; e < ntot; e += blockDim.x) { s_kx[e] = A.x[lfirst + e]; s_ki[e] = A.idx[lfirst + e]; }
+            __syncthreads();
+            // every thread carries up to two elements: read all their fields, rank them, write them back
+            double f[2][9];
+            unsigned fi[2];
+            int dest[2] = {-1, -1};
+            for (int q = 0; q < 2; q++) {
+                const int e = threadIdx.x + q * blockDim.x;
+                if (e >= ntot) continue;
+                const int sl = lfirst + e;
+                f[q][0] = A.x[sl]; f[q][1] = A.m[sl]; f[q][2] = A.vh[sl]; f[q][3] = A.uh[sl]; f[q][4] = A.vn[sl];
+                f[q][5] = A.un[sl]; f[q][6] = A.h[sl]; f[q][7] = A.rho[sl]; f[q][8] = A.P[sl];
+                fi[q] = A.idx[sl];
+                int rank = 0;
+                const double xe = s_kx[e];
+                const unsigned ie = s_ki[e];
+                for (int g = 0; g < ntot; g++) rank += (s_kx[g] < xe || (s_kx[g] == xe && s_ki[g] < ie)) ? 1 : 0;
+                dest[q] = lfirst + rank;
+                if ((e < nleft) != (rank < nleft)) atomicAdd(&ctl->migrated, 1);
+            }
+            __syncthreads();
+            for (int q = 0; q < 2; q++) {
+                if (dest[q] < 0) continue;
+                const int sl = dest[q];
+                A.x[sl] = f[q][0]; A.m[sl] = f[q][1]; A.vh[sl] = f[q][2]; A.uh[sl] = f[q][3]; A.vn[sl] = f[q][4];
+                A.un[sl] = f[q][5]; A.h[sl] = f[q][6]; A.rho[sl] = f[q][7]; A.P[sl] = f[q][8];
+                A.idx[sl] = fi[q];
+            }
+            __syncthreads();
+            // deeper than the window?  then the own block is no longer sorted where the window begins / ends
+            if (threadIdx.x == 0) {
+                const int own0 = A.side < 0 ? A.pad : A.pad + A.na - ko;
+                const bool bad = A.side < 0 ? (ko < A.na && A.x[own0 + ko - 1] > A.x[own0 + ko])
+                                            : (ko < A.na && A.x[own0 - 1] > A.x[own0]);
+                if (bad) raise(ctl, E_UNSORTED, own0);
+            }
         }
     }
     if (what == MSG_ITERATE && s_changed) {

@@ -103,6 +103,26 @@ class SlabRank(Simulation):
         return [flags[0], flags[1], flags[2]]
 
 
+def _fields_by_index(ranks):
+    """Records of the given ranks' handles: alive particles sorted by their global index (a slab's records
+    travel in x order with the index in `id`, and particles may have changed slab), then the wall ghosts."""
+    import numpy as np
+    from .api import FIELDS
+    alive, ghosts = [], []
+    for r in ranks:
+        rec, g = r.download()
+        na = len(rec) - g
+        alive.append(rec[:na].copy())
+        ghosts.append(rec[na:].copy())
+    a = np.concatenate(alive)
+    a = a[np.argsort(a["id"], kind="stable")]
+    gh = np.concatenate(ghosts)
+    rec = np.concatenate([a, gh])
+    f = np.stack([rec[name] for name in FIELDS], axis=1)
+    t = rec["type"].astype(np.int32)
+    return f, t, len(gh), a["id"].astype(np.int64)
+
+
 class LocalTransport:
     """All ranks live in this process (one device): a message is a device-to-device copy."""
 
@@ -283,19 +303,9 @@ class SlabSimulation:
         return self.ranks[0].counters()
 
     def fields(self):
-        """Alive particles of the local ranks in global index order, then their wall ghosts."""
-        import numpy as np
-        alive, ghosts, types = [], [], []
-        for r in self.ranks:
-            f, t, g = r.fields()
-            na = f.shape[0] - g
-            alive.append(f[:na])
-            ghosts.append(f[na:])
-        f = np.concatenate(alive + ghosts)
-        ng = sum(g.shape[0] for g in ghosts)
-        t = np.zeros(f.shape[0], dtype=np.int32)
-        t[f.shape[0] - ng:] = 1
-        return f, t, ng
+        """([n, 9] doubles, type[n], n_ghost, global index[n_alive]) of the local ranks: alive particles in
+        ascending global index, then the wall ghosts."""
+        return _fields_by_index(self.ranks)
 
     def close(self):
         for r in self.ranks:
@@ -346,7 +356,7 @@ class NativeSlabSimulation:
         return self.ranks[0].counters()
 
     def fields(self):
-        return self.ranks[0].fields()
+        return _fields_by_index(self.ranks)
 
     def close(self):
         self.ranks[0].close()

@@ -34,10 +34,10 @@ def main():
             sim.step(1)
         if st in (0, 1, 3, 6):
             f1 = one.fields()[0]
-            f2, _, g2 = sim.fields()
+            f2, _, g2, ids = sim.fields()
             r = sim.ranks[0]
-            na = r.i1 - r.i0
-            same = np.array_equal(f1[r.i0:r.i1], f2[:na])
+            na = len(ids)
+            same = np.array_equal(f1[ids], f2[:na])
             print("rank %d step %d: slab [%d, %d) %s, rounds %d" % (rank, st, r.i0, r.i1,
                                                                    "identical" if same else "DIFFERS", sim.rounds_last),
                   "(native)" if native else "(torch.distributed)", flush=True)

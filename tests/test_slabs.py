@@ -112,7 +112,7 @@ def test_slabs_in_one_process_match_single_handle_bit_for_bit(n, pc, varh, world
             many.step(1)
         if st in (0, 1, 4, 8):
             f1, t1, g1 = one.fields()
-            f2, t2, g2 = many.fields()
+            f2, t2, g2, ids = many.fields()
             assert g1 == g2 and f1.shape == f2.shape
             # alive particles: everything; wall ghosts: all but the dead acc/du_dt of t = 0
             assert np.array_equal(f1[:n], f2[:n]), "step %d: %s" % (st, np.argwhere(f1[:n] != f2[:n])[:4])
@@ -153,3 +153,38 @@ def test_slabs_over_nccl_match_single_handle(native):
                          env=dict(os.environ, SLAB_NATIVE=native))
     assert res.returncode == 0, res.stdout[-3000:]
     assert "DIFFERS" not in res.stdout
+
+
+@pytest.mark.gpu
+def test_particles_crossing_a_slab_edge_change_owner():
+    """Two particles either side of the slab edge are thrown at each other so that they swap places in one
+    step: both ranks merge-split the particles around the edge (no extra message), the particle counts stay
+    equal, and the run stays bit-identical to the single-handle run (which re-sorts)."""
+    from sph_b200 import Simulation
+    from sph_b200.slabs import make_local_slabs
+    n, world = 4000, 2
+    cfg = _cfg(n, 1)
+    ref = Simulation(cfg)
+    ref.init_lattice()
+    rec, ng = ref.download()
+    rec = rec[:n].copy()                 # alive particles only, array order = x order = global index
+    rec["id"] = np.arange(n)
+    rec["vel"][n // 2 - 1] = 5.0         # last particle of slab 0 ...
+    rec["vel"][n // 2] = -5.0            # ... and first of slab 1 approach by more than one spacing per step
+    ref.upload(rec.copy(), 0)
+    many = make_local_slabs(cfg, world, halo_count=64)
+    for r in many.ranks:
+        r.upload(rec[r.i0:r.i1].copy(), 0)
+    for st in (1, 2, 3):
+        ref.step(1)
+        many.step(1)
+        f1 = ref.fields()[0]
+        f2, t2, g2, ids = many.fields()
+        assert np.array_equal(ids, np.arange(n))
+        assert np.array_equal(f1[:n], f2[:n]), "step %d: %s" % (st, np.argwhere(f1[:n] != f2[:n])[:4])
+    # the two particles now live on the other rank
+    own0 = set(many.ranks[0].download()[0]["id"][: n // 2].tolist())
+    assert (n // 2) in own0 and (n // 2 - 1) not in own0
+    assert ref.counters().sorts >= 1
+    ref.close()
+    many.close()
