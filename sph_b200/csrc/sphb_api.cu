@@ -621,13 +621,15 @@ __global__ void k_flags(const Ctl *ctl, int *flags) {
     flags[2] = ctl->halo_changed;
 }
 
-// pack both edges, one grouped send/recv with the neighbours, unpack both pads
+// pack both edges (one launch), one grouped send/recv with the neighbours, unpack both pads (one launch)
 int native_exchange(sphb_handle *H, int what) {
     const int n = sphb_slab_message_doubles(H, what);
-    for (int k = 0; k < 2; k++) {
-        const int side = k ? 1 : -1;
-        if (k ? H->halo_r : H->halo_l) TRY(sphb_slab_pack(H, what, side, H->msg_send[what][k]));
-    }
+    SlabArgs A = slab_args(H, 0);
+    if (what == MSG_BASE && !H->ghost_in_half) { A.vh = H->v; A.uh = H->u; }   // t = 0: the current v, u
+    k_slab_pack2<<<dim3(std::max(1, std::min(nblk(H->K, 256), 32)), 2), 256, 0, H->stream>>>(
+        A, what, H->halo_l ? H->msg_send[what][0] : nullptr, H->halo_r ? H->msg_send[what][1] : nullptr);
+    H->launches++;
+    CK(cudaGetLastError());
     NK(g_nccl.GroupStart());
     for (int k = 0; k < 2; k++) {
         if (!(k ? H->halo_r : H->halo_l)) continue;
@@ -636,10 +638,10 @@ int native_exchange(sphb_handle *H, int what) {
         NK(g_nccl.Recv(H->msg_recv[what][k], (size_t)n, ncclFloat64, peer, H->comm, H->stream));
     }
     NK(g_nccl.GroupEnd());
-    for (int k = 0; k < 2; k++) {
-        const int side = k ? 1 : -1;
-        if (k ? H->halo_r : H->halo_l) TRY(sphb_slab_unpack(H, what, side, H->msg_recv[what][k]));
-    }
+    k_slab_unpack2<<<2, 1024, 0, H->stream>>>(A, what, H->halo_l ? H->msg_recv[what][0] : nullptr,
+                                              H->halo_r ? H->msg_recv[what][1] : nullptr);
+    H->launches++;
+    CK(cudaGetLastError());
     return SPHB_OK;
 }
 

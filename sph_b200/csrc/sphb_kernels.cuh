@@ -1047,7 +1047,7 @@ struct SlabArgs {
 };
 
 // my edge particles -> message (side = which of my edges)
-__global__ void k_slab_pack(SlabArgs A, int what, double *buf) {
+__device__ __forceinline__ void slab_pack_body(const SlabArgs &A, int what, double *buf) {
     const int cnt = min(A.K, A.na);
     const int first = A.side < 0 ? A.pad : A.pad + A.na - cnt;
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < cnt; k += gridDim.x * blockDim.x) {
@@ -1070,8 +1070,17 @@ __global__ void k_slab_pack(SlabArgs A, int what, double *buf) {
     }
 }
 
+__global__ void k_slab_pack(SlabArgs A, int what, double *buf) { slab_pack_body(A, what, buf); }
+// both edges in one launch: blockIdx.y = 0 left, 1 right; a null buffer = no neighbour on that side
+__global__ void k_slab_pack2(SlabArgs A, int what, double *buf_l, double *buf_r) {
+    double *buf = blockIdx.y ? buf_r : buf_l;
+    if (!buf) return;
+    A.side = blockIdx.y ? 1 : -1;
+    slab_pack_body(A, what, buf);
+}
+
 // message from the neighbour on `side` -> my pad on that side.  One CTA.
-__global__ void __launch_bounds__(1024) k_slab_unpack(SlabArgs A, int what, const double *buf) {
+__device__ __forceinline__ void slab_unpack_body(const SlabArgs &A, int what, const double *buf) {
     Ctl *ctl = A.ctl;
     const int cnt = (int)buf[msg_rows(what) * A.K];
     if (cnt < 0 || cnt > A.K || cnt > A.pad) {
@@ -1202,6 +1211,17 @@ __global__ void __launch_bounds__(1024) k_slab_unpack(SlabArgs A, int what, cons
         }
         if (threadIdx.x == 0) ctl->halo_changed = 1;
     }
+}
+
+__global__ void __launch_bounds__(1024) k_slab_unpack(SlabArgs A, int what, const double *buf) {
+    slab_unpack_body(A, what, buf);
+}
+// both pads in one launch: one CTA per side (blockIdx.x = 0 left, 1 right); a null buffer = no neighbour
+__global__ void __launch_bounds__(1024) k_slab_unpack2(SlabArgs A, int what, const double *buf_l, const double *buf_r) {
+    const double *buf = blockIdx.x ? buf_r : buf_l;
+    if (!buf) return;
+    A.side = blockIdx.x ? 1 : -1;
+    slab_unpack_body(A, what, buf);
 }
 
 __global__ void k_slab_flags(Ctl *ctl, int hl, int hr) { ctl->halo_left = hl; ctl->halo_right = hr; }
