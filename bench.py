@@ -274,7 +274,9 @@ def run_ours(args, name, n, pc, varh):
     newton_mean = sum(k * v for k, v in enumerate(hist)) / tot if varh else 0.0
     nbr_rho = c2.nbr_mean
     nbr_f = max(c2.force_pairs_mean - 1.0, 0.0)
-    passes = (1.0 + newton_mean) if varh else 1.0
+    # neighbour-window scans actually made per particle (1 + Newton iterations, minus the last one wherever the
+    # final Newton step was below 1e-12 and the previous sums were reused)
+    passes = c2.density_scans_mean if c2.density_scans_mean > 0 else ((1.0 + newton_mean) if varh else 1.0)
     # algorithmic bytes per particle: density kernel reads x,h,rho and writes
     # h,rho,omega_new,omega_stale (56 B) + 8 B (x_j) per neighbour per pass of the root-find
     bytes_density = (56.0 if varh else 24.0) + 8.0 * passes * nbr_rho

@@ -82,6 +82,8 @@ typedef struct sphb_counters {
     double h_max;
     long long launches;         /* kernels this handle has launched (CUB's sort kernels not counted) */
     double force_pairs_mean;    /* most recent step: (i,j) pairs per particle in the first force sweep, self included */
+    double density_scans_mean;  /* most recent density pass: neighbour-window scans per particle (1 + Newton iterations, minus
+                                   the final one where the last Newton step was below 1e-12 and the sums were reused) */
     int refine_tiles;           /* most recent step: tiles the ordered-sweep refinement took from its work lists */
     int refine_tile_evals;      /* ... and how often it evaluated them, in-tile iterations included */
 } sphb_counters;

@@ -45,7 +45,7 @@ class SphbCounters(C.Structure):
                 ("fallbacks", C.c_longlong), ("newton_hist", C.c_longlong * 12),
                 ("nbr_min", C.c_int), ("nbr_max", C.c_int), ("nbr_mean", C.c_double),
                 ("h_max", C.c_double), ("launches", C.c_longlong), ("force_pairs_mean", C.c_double),
-                ("refine_tiles", C.c_int), ("refine_tile_evals", C.c_int)]
+                ("density_scans_mean", C.c_double), ("refine_tiles", C.c_int), ("refine_tile_evals", C.c_int)]
 
 
 assert C.sizeof(SphbConfig) == 64
@@ -84,6 +84,7 @@ class Counters:
     h_max: float
     launches: int = 0
     force_pairs_mean: float = 0.0
+    density_scans_mean: float = 0.0
     refine_tiles: int = 0
     refine_tile_evals: int = 0
 
@@ -298,7 +299,7 @@ class Simulation:
         self._check(self.L.sphb_get_counters(self.h, C.byref(c)))
         return Counters(c.n_alive, c.n_ghost, c.steps, c.sweeps_total, c.sweeps_last, c.sorts,
                         c.fallbacks, list(c.newton_hist), c.nbr_min, c.nbr_max, c.nbr_mean, c.h_max,
-                        c.launches, c.force_pairs_mean, c.refine_tiles, c.refine_tile_evals)
+                        c.launches, c.force_pairs_mean, c.density_scans_mean, c.refine_tiles, c.refine_tile_evals)
 
     def set_profiling(self, on=True):
         self._check(self.L.sphb_set_profiling(self.h, int(on)))

@@ -1288,7 +1288,10 @@ int sphb_get_counters(sphb_handle *H, sphb_counters *out) {
     out->h_max = 0.0;
     { long long b = (long long)H->h_ctl->hmax_bits; memcpy(&out->h_max, &b, sizeof(double)); }
     out->launches = H->launches;
-    out->force_pairs_mean = H->na ? (double)H->h_ctl->force_pairs / H->na : 0.0;
+    unsigned long long pairs = 0, scans = 0;
+    for (int b = 0; b < kStatBins; b++) { pairs += H->h_ctl->force_pairs[b]; scans += H->h_ctl->density_scans[b]; }
+    out->force_pairs_mean = H->na ? (double)pairs / H->na : 0.0;
+    out->density_scans_mean = (H->na + out->n_ghost) ? (double)scans / (H->na + H->h_ctl->GL + H->h_ctl->GR) : 0.0;
     out->refine_tiles = H->h_ctl->tiles_swept;
     out->refine_tile_evals = H->h_ctl->tile_evals;
     if (H->have_counts) {

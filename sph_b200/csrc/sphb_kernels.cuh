@@ -43,6 +43,8 @@ enum ErrCode {
 };
 
 // Device control block (one per handle), read back by the host at sync points.
+constexpr int kStatBins = 64;
+
 struct Ctl {
     int GL, GR;                    // ghosts currently in the left / right pad
     int ncand;                     // ghost candidates appended this step
@@ -60,7 +62,10 @@ struct Ctl {
     int halo_changed;              // an incoming halo iterate differed from the copy held here
     int migrated;                  // particles that changed slab in the current attempt
     int mass_differs;              // upload: some particle's mass is not the first particle's (cleared by the upload)
-    unsigned long long force_pairs; // (i,j) pairs evaluated by the first force sweep (self included)
+    // statistics, one atomic per warp spread over kStatBins addresses (a single address would serialise
+    // two million atomics per launch and cost more than a millisecond at 64 Mi particles)
+    unsigned long long force_pairs[kStatBins];   // (i,j) pairs evaluated by the first force sweep (self included)
+    unsigned long long density_scans[kStatBins]; // neighbour-window scans of the most recent density pass
 };
 
 __device__ __forceinline__ void raise(Ctl *ctl, int code, int particle) {
@@ -111,6 +116,7 @@ struct __align__(64) Rec2 { Rec A, B; };   // new state (as seen once the sweep 
 
 constexpr int kDHalo = 64;    // density pass: x staged on each side of a tile
 constexpr int kFHalo = 32;    // force pass: neighbour state staged on each side of a tile
+constexpr double kTinyStep = 1e-12;  // Newton step below which the sums of the previous evaluation stand for the new h
 constexpr int kMergeMax = 1024;  // largest halo_count for which a cross-edge merge-split is done on the device
 constexpr int kLocalIters = 48;  // cap on the in-tile iterations of one refinement sweep
 
@@ -256,6 +262,7 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
 
     const int s = t0 + threadIdx.x;
     double hloc = 0.0;
+    int npass = 0;               // window scans this thread made (statistics: the algorithmic bytes of the pass)
     // pad slots that hold another slab's particles get everything from their owner
     const bool halo_slot = SLAB && ((s < A.pad && ctl->halo_left) || (s >= A.pad + A.na && ctl->halo_right));
     if (s >= lo && s < hi && !halo_slot) {
@@ -268,9 +275,12 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
         const int npart = A.na + ctl->GL + ctl->GR;
         double hnew = hold, rhonew = rhoold, om_new = 1.0, om_stale = 1.0;
         int iters = 0, cnt = 0;
+        bool tiny = false;
+        (void)tiny;
         double Sw, Sg, Sgr = 0.0;
 #define SPHB_EVAL(H_, F_, DF_, DSUM_)                                                           \
     {                                                                                           \
+        npass++;                                                                                \
         density_sums<UM>(ctl, SLAB && !is_pad, sx, wbase, wn, A.x, A.m, s, lo, hi, xi, (H_), Sw, Sg, Sgr, cnt); \
         const double ih_ = 1.0 / (H_), ih2_ = ih_ * ih_, ih4_ = ih2_ * ih2_;                    \
         const double rho_ = mi * (kSigma * (Sw * (ih4_ * ih_)));                                \
@@ -293,6 +303,18 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
                     iters++;
                     if (df == 0.0) { raise(ctl, E_ZERO_DERIVATIVE, s); break; }
                     const double xn = xcur - f / df;
+                    if (fabs(xn - xcur) <= kTinyStep * fabs(xn)) {
+                        // The step did not move h beyond 1e-12 relative: this iteration passes the stop test
+                        // (1e-4), and what GSL evaluates at xn is not used for another step.  The sums at xn
+                        // equal the sums just taken at xcur to within 1e-12 (the density to ~1e-24 with its
+                        // first-order term), five orders below the parity tolerance: do not walk the window
+                        // again.  (Iteration count, returned h and stop decision are exactly the reference's.)
+                        if (UM) rho_cur = fma(-dsum, xcur - xn, rho_cur);     // rho(xn) = rho(xcur) + drho/dh (xn - xcur)
+                        xcur = xn;
+                        cont = false;
+                        tiny = true;
+                        break;
+                    }
                     SPHB_EVAL(xn, f, df, dsum);
                     if (!isfinite(f) || !isfinite(df)) { raise(ctl, E_NOT_FINITE, s); break; }
                     const double xprev = xcur;
@@ -379,6 +401,13 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
         // touches, in whichever state (new, or old when check_old) it will be seen
         if (rhonew < kEps || (A.check_old && rhoold < kEps)) raise(ctl, E_LOW_DENSITY, s);
         hloc = fmax(hnew, hold);
+    }
+    // window scans of this tile (one atomic per warp)
+    {
+        int np = npass;
+        for (int o = 16; o > 0; o >>= 1) np += __shfl_xor_sync(0xffffffffu, np, o);
+        if ((threadIdx.x & 31) == 0 && np)
+            atomicAdd(&ctl->density_scans[(blockIdx.x * (kTile / 32) + (threadIdx.x >> 5)) % kStatBins], (unsigned long long)np);
     }
     // block max of h -> global upper bound for the force pass window
     __shared__ double smax[kTile / 32];
@@ -722,7 +751,8 @@ __global__ void __launch_bounds__(kTile, 4) k_force_first(SweepArgs A) {
     force_tile<SEL, ADIA, UM, true>(A, tile, lo, hi, Hb, A.epoch, changed, npairs);
     // pair statistics for the roofline accounting (one atomic per warp)
     for (int o = 16; o > 0; o >>= 1) npairs += __shfl_xor_sync(0xffffffffu, npairs, o);
-    if ((threadIdx.x & 31) == 0 && npairs) atomicAdd(&ctl->force_pairs, (unsigned long long)npairs);
+    if ((threadIdx.x & 31) == 0 && npairs)
+        atomicAdd(&ctl->force_pairs[(blockIdx.x * (kTile / 32) + (threadIdx.x >> 5)) % kStatBins], (unsigned long long)npairs);
 }
 
 // Refinement of the ordered sweep: ONE persistent cooperative launch that repeats
@@ -1288,7 +1318,7 @@ __global__ void k_begin(Ctl *ctl, int clear_cand) {
     ctl->tile_evals = 0;
     ctl->tiles_swept = 0;
     ctl->halo_changed = 0;
-    ctl->force_pairs = 0ull;
+    for (int b = 0; b < kStatBins; b++) { ctl->force_pairs[b] = 0ull; ctl->density_scans[b] = 0ull; }
 }
 
 }  // namespace sphb
