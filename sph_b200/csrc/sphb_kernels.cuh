@@ -278,6 +278,9 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
         bool tiny = false;
         (void)tiny;
         double Sw, Sg, Sgr = 0.0;
+        // 1/h, h and sum_j m_j dW/dh of the first and of the most recent evaluation: the records below are built
+        // from them without further divisions by h
+        double ih_last = 0.0, x_last = 0.0, dsum_last = 0.0, ih_first = 0.0, x_first = 0.0, dsum_first = 0.0;
 #define SPHB_EVAL(H_, F_, DF_, DSUM_)                                                           \
     {                                                                                           \
         npass++;                                                                                \
@@ -288,13 +291,15 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
         DSUM_ = UM ? -(mi * (kSigma * (Sg * (ih4_ * ih2_)))) : -(kSigma * (Sg * (ih4_ * ih2_))); \
         DF_ = DSUM_ + mi * A.hfac * ih2_;                                                       \
         rho_cur = rho_;                                                                         \
+        ih_last = ih_; x_last = (H_); dsum_last = DSUM_;                                        \
     }
         (void)msig;
         if (VARH) {
             const double x0 = hold > kEps ? hold : A.hfac * (2 * A.limit / (npart - 1));
             double f, df, dsum, rho_cur;
             SPHB_EVAL(x0, f, df, dsum);
-            om_stale = 1.0 - dsum * (-hold / rhoold);
+            ih_first = ih_last; x_first = x_last; dsum_first = dsum_last;
+            if (A.oms) om_stale = 1.0 - dsum * (-hold / rhoold);
             if (do_root) {
                 double xcur = x0;
                 bool cont = true;
@@ -365,13 +370,14 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
                 if (xcur < 0) raise(ctl, E_NEGATIVE_H, s);
                 hnew = xcur;
                 rhonew = rho_cur;
-                om_new = 1.0 - dsum * (-hnew / rhonew);
+                if (A.omn) om_new = 1.0 - dsum * (-hnew / rhonew);
             } else {
                 om_new = om_stale;   // particle keeps its stored h, rho: omega for those
             }
         } else {
             double f, df, dsum, rho_cur;
             SPHB_EVAL(hold, f, df, dsum);
+            ih_first = ih_last; x_first = x_last; dsum_first = 0.0; dsum_last = 0.0;   // fixed h: omega = 1
             (void)f; (void)df; (void)dsum;
             if (is_pad ? A.root_ghosts : A.root_alive) rhonew = rho_cur;
         }
@@ -380,14 +386,20 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
         A.rhon[s] = rhonew;
         if (A.omn) { A.omn[s] = om_new; A.oms[s] = om_stale; }
         if (A.rec) {
-            // c5 = -4 sigma / h^5 and kap = 1 / (rho omega): the only divisions the force pass would need
-            const double ihn = 1.0 / hnew, ihn2 = ihn * ihn;
+            // c5 = -4 sigma / h^5 and kap = 1 / (rho omega) = 1 / (rho + h sum_j m_j dW/dh): the divisions the
+            // force pass would otherwise make per pair.  1/h is at hand from the evaluations (one Newton step of
+            // the reciprocal covers an h that moved by less than 1e-12 since its last evaluation).
+            double ihn = ih_last;
+            if (hnew != x_last) ihn = fma(ihn, fma(-hnew, ihn, 1.0), ihn);
+            const double ihn2 = ihn * ihn;
             Rec2 r2;
-            r2.A.h = hnew; r2.A.c5 = kGradC * ((ihn2 * ihn2) * ihn); r2.A.rho = rhonew; r2.A.kap = 1.0 / (rhonew * om_new);
+            r2.A.h = hnew; r2.A.c5 = kGradC * ((ihn2 * ihn2) * ihn); r2.A.rho = rhonew;
+            r2.A.kap = 1.0 / fma(hnew, (do_root ? dsum_last : dsum_first), rhonew);
             r2.B = r2.A;
             if (VARH && A.check_old) {
-                const double iho = 1.0 / hold, iho2 = iho * iho;
-                r2.B.h = hold; r2.B.c5 = kGradC * ((iho2 * iho2) * iho); r2.B.rho = rhoold; r2.B.kap = 1.0 / (rhoold * om_stale);
+                const double iho = (hold == x_first) ? ih_first : 1.0 / hold, iho2 = iho * iho;
+                r2.B.h = hold; r2.B.c5 = kGradC * ((iho2 * iho2) * iho); r2.B.rho = rhoold;
+                r2.B.kap = 1.0 / fma(hold, dsum_first, rhoold);
             } else if (A.check_old) {
                 r2.B.rho = rhoold; r2.B.kap = 1.0 / rhoold;      // fixed h: omega = 1, h unchanged
             }
