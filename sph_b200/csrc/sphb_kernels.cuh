@@ -536,6 +536,7 @@ struct ForceSmem {
     double vA[kTile + 2 * kFHalo], uA[kTile + 2 * kFHalo];
     double vB[kTile + 2 * kFHalo], uB[kTile + 2 * kFHalo];
     unsigned idx[kTile + 2 * kFHalo];
+    double gsum[kTile], pst[kTile];      // own particles: gradient sum of the density pass, stored pressure
 };
 
 template <bool VOL>
@@ -652,6 +653,10 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
         S.uB[k] = __ldg(A.F.uB + j);
         if (!FIRST) { S.vA[k] = ldv<true>(A.F.vA + j); S.uA[k] = ldv<true>(A.F.uA + j); }
     }
+    if (t0 + (int)threadIdx.x < tend) {   // issued with the staging loads, read after the pair loops
+        S.gsum[threadIdx.x] = A.F.gsum[t0 + threadIdx.x];
+        S.pst[threadIdx.x] = A.Pstale[t0 + threadIdx.x];
+    }
     if (threadIdx.x == 0) { sx[-1] = -INFINITY; sx[wn] = INFINITY; }
     __syncthreads();
 
@@ -666,11 +671,11 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
         if (s < tend) {
             const int ks2 = s - wbase;
             Own<ADIA> o;
-            const double vi = A.vh[s], ui = A.uh[s];
+            const double vi = S.vB[ks2], ui = S.uB[ks2];      // = A.vh[s], A.uh[s]: staged with the tile
             {
                 Rec ro;
                 ro.h = S.hc[0][ks2].x; ro.c5 = S.hc[0][ks2].y; ro.rho = S.rk[0][ks2].x; ro.kap = S.rk[0][ks2].y;
-                o.set(sx[ks2], S.idx[ks2], ro, vi, ui, A.Pstale[s]);
+                o.set(sx[ks2], S.idx[ks2], ro, vi, ui, S.pst[threadIdx.x]);
             }
             const double reach2 = kRadius * Hb;
             double a_sum = 0.0, e_sum = 0.0;
@@ -679,7 +684,7 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
             force_side<SEL, ADIA, UM, true, -1>(A, S, o, ks2, wbase, wn, lo, hi, reach2, a_sum, e_sum, npairs, jmin);
             force_side<SEL, ADIA, UM, true, +1>(A, S, o, ks2, wbase, wn, lo, hi, reach2, a_sum, e_sum, npairs, jmax);
             if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
-            a_sum = fma(-o.PrRho, A.F.gsum[s], a_sum);        // - P_i/(rho_i^2 om_i) sum_j m_j gradW_ij(h_i)
+            a_sum = fma(-o.PrRho, S.gsum[threadIdx.x], a_sum);   // - P_i/(rho_i^2 om_i) sum_j m_j gradW_ij(h_i)
             if (!A.kick) {
                 A.a[s] = a_sum;
                 A.du[s] = e_sum;
@@ -706,10 +711,10 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
         Own<ADIA> o;
         double vi = 0.0, ui = 0.0, gsum = 0.0, vscale = 1.0;
         if (active) {
-            vi = A.vh[s]; ui = A.uh[s]; gsum = A.F.gsum[s];
+            vi = S.vB[ks]; ui = S.uB[ks]; gsum = S.gsum[threadIdx.x];
             Rec ro;
             ro.h = S.hc[0][ks].x; ro.c5 = S.hc[0][ks].y; ro.rho = S.rk[0][ks].x; ro.kap = S.rk[0][ks].y;
-            o.set(sx[ks], S.idx[ks], ro, vi, ui, A.Pstale[s]);
+            o.set(sx[ks], S.idx[ks], ro, vi, ui, S.pst[threadIdx.x]);
             vscale = fmax(fabs(vi), o.c_ec);   // velocities pass through zero: judge them against max(|v|, c_s)
         }
         double a_sum = 0.0, e_sum = 0.0, vf = 0.0, uf = 0.0;
