@@ -247,7 +247,10 @@ struct DensityArgs {
 // With f(h) = m_i sigma Sw / h^5 - m_i hf / h and f'(h) = -sigma Sg / h^6 + m_i hf / h^2.
 // SLAB: pads may hold another slab's particles and the launch may cover a subset of the tiles
 template <bool VARH, bool UM, bool SLAB>
-__global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
+#ifndef SPHB_DENS_BLOCKS
+#define SPHB_DENS_BLOCKS 6
+#endif
+__global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs A) {
     __shared__ double sxs[kTile + 2 * kDHalo + 2];
     double *sx = sxs + 1;
     Ctl *ctl = A.ctl;
@@ -416,20 +419,23 @@ __global__ void __launch_bounds__(kTile, 5) k_density(DensityArgs A) {
     }
     // window scans of this tile (one atomic per warp)
     {
-        int np = npass;
-        for (int o = 16; o > 0; o >>= 1) np += __shfl_xor_sync(0xffffffffu, np, o);
+        const int np = __reduce_add_sync(0xffffffffu, npass);
         if ((threadIdx.x & 31) == 0 && np)
             atomicAdd(&ctl->density_scans[(blockIdx.x * (kTile / 32) + (threadIdx.x >> 5)) % kStatBins], (unsigned long long)np);
     }
-    // block max of h -> global upper bound for the force pass window
-    __shared__ double smax[kTile / 32];
-    for (int o = 16; o > 0; o >>= 1) hloc = fmax(hloc, __shfl_xor_sync(0xffffffffu, hloc, o));
-    if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = hloc;
+    // Block max of h -> global upper bound for the force pass window.  It is only a scan bound, so it
+    // may be rounded UP to single precision: positive floats order like their bit patterns, which makes
+    // the warp step one REDUX instruction instead of five 64-bit shuffle / select rounds.
+    __shared__ unsigned smax[kTile / 32];
+    const unsigned wmax = __reduce_max_sync(0xffffffffu, __float_as_uint(__double2float_ru(hloc)));
+    if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = wmax;
     __syncthreads();
     if (threadIdx.x == 0) {
-        double mx = smax[0];
-        for (int k = 1; k < kTile / 32; k++) mx = fmax(mx, smax[k]);
-        atomicMax(&ctl->hmax_bits, (unsigned long long)__double_as_longlong(mx));
+        unsigned mx = smax[0];
+        for (int k = 1; k < kTile / 32; k++) mx = max(mx, smax[k]);
+        const unsigned long long bits = (unsigned long long)__double_as_longlong((double)__uint_as_float(mx));
+        // after the first CTAs the bound rarely grows: look before paying for an atomic on one hot address
+        if (bits > *((volatile unsigned long long *)&ctl->hmax_bits)) atomicMax(&ctl->hmax_bits, bits);
     }
 }
 
@@ -767,7 +773,7 @@ __global__ void __launch_bounds__(kTile, 4) k_force_first(SweepArgs A) {
     const int tile = MAPPED ? (int)blockIdx.x + A.tile_base : (int)blockIdx.x;
     force_tile<SEL, ADIA, UM, true>(A, tile, lo, hi, Hb, A.epoch, changed, npairs);
     // pair statistics for the roofline accounting (one atomic per warp)
-    for (int o = 16; o > 0; o >>= 1) npairs += __shfl_xor_sync(0xffffffffu, npairs, o);
+    npairs = __reduce_add_sync(0xffffffffu, npairs);
     if ((threadIdx.x & 31) == 0 && npairs)
         atomicAdd(&ctl->force_pairs[(blockIdx.x * (kTile / 32) + (threadIdx.x >> 5)) % kStatBins], (unsigned long long)npairs);
 }
