@@ -48,3 +48,19 @@ def test_invalid_arguments_are_rejected_before_touching_the_device():
     cfg = api.SphbConfig(101, 0.04, 7, 2.0, 1.0, 2.0, 0.005, 0)
     assert L.sphb_create(C.byref(cfg), None, C.byref(h)) == 1
     assert b"Unknown pressure calculation mode" in L.sphb_last_error(None)
+
+
+def test_ctypes_structs_match_the_c_header(tmp_path):
+    """include/sphb.h compiles as plain C99 and its struct sizes are the ones the ctypes binding assumes."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include "sphb.h"\nint main(void){printf("%zu %zu %zu %zu\\n", sizeof(sphb_config), '
+                   'sizeof(sphb_particle), sizeof(sphb_options), sizeof(sphb_counters));return 0;}\n')
+    exe = tmp_path / "sizes"
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror",
+                           "-I" + os.path.join(root, "include"), str(src), "-o", str(exe)])
+    sizes = [int(v) for v in subprocess.check_output([str(exe)]).decode().split()]
+    assert sizes == [C.sizeof(api.SphbConfig), api.PARTICLE_DTYPE.itemsize, C.sizeof(api.SphbOptions),
+                     C.sizeof(api.SphbCounters)]
