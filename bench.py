@@ -13,8 +13,9 @@ One JSON line on stdout (rank 0):
   value      whole-job particle-steps/s, state resident in HBM, CUDA events on the launching stream
   e2e        same metric through the host-facing C-ABI route with HOST buffers every step:
              sphb_upload (pinned AoS Particle[] -> device) + sphb_step(1) + sphb_download
-  roofline   dominant kernel (fused density/root-find/omega): algorithmic bytes per launch ÷ its
-             CUDA-event duration, against MEASURED_PEAKS.json's HBM copy bandwidth
+  roofline   dominant kernel (the longer of the fused density pass and the first force sweep): algorithmic
+             bytes per launch ÷ its CUDA-event duration, against MEASURED_PEAKS.json's HBM copy bandwidth;
+             `traffic` = ncu dram bytes of that kernel (profiles/), next to the whole-step fractions
   cpu_baseline  the plain-C O(N k) port of the reference (oracle/) timed on one host core on a
              bounded sample of the same workload
 --impl reference times the reference's own code (oracle/_ref, built from /root/reference by
@@ -116,7 +117,7 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------
 # CPU legs (the only places bench.py may execute oracle/)
 
-def cpu_port_baseline(pc, varh, sample_n=400_001, steps=3):
+def cpu_port_baseline(pc, varh, sample_n=600_001, steps=4):
     """The O(N k) plain-C port (oracle/sph_oracle.c), one thread, same generator at sample_n."""
     from oracle.sph_oracle import Oracle
     kw = workload_kwargs(sample_n, pc, varh)
@@ -376,7 +377,7 @@ def run_ours(args, name, n, pc, varh):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
