@@ -302,7 +302,7 @@ def run_ours(args, name, n, pc, varh):
         pass
     roofline = {"bound": "hbm", "kernel": kname,
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "profiles/traffic_r01.json: ncu dram__bytes_read+write per launch at N = 16 Mi, scaled per particle",
+                "traffic_source": "profiles/traffic_r01.json: ncu dram__bytes_read+write per launch at N = 64 Mi (--set full), scaled per particle",
                 "peak_source": peak_src, "bytes_per_particle": dom[2], "launch_ms": dom[1],
                 "step_b_ns_bytes_per_particle": b_ns,
                 "step_frac_b_ns": value / world * b_ns / 1e9 / peak,
