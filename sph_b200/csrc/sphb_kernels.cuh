@@ -88,19 +88,26 @@ __device__ __forceinline__ double clamp2(double t) { return t + fabs(t); }   // 
 // of t_k (an integer test of the high word, off the FP64 pipe) instead of clamping: a neighbour in
 // the outer shell costs 4 FP64 operations here, not 15.  Neighbouring lanes hold neighbouring
 // particles with nearly the same h and spacing, so the branches rarely diverge.
-__device__ __forceinline__ double dpoly_from(double t1, double r, double h, double k2, double k3) {
+__device__ __forceinline__ double dpoly_from(double t1, double r, double h, double k2, double k3, int hi_eps) {
     double p = 0.0;
-    if (__double2hiint(t1) >= 0) {
+    if (__double2hiint(t1) >= hi_eps) {
         p = (t1 * t1) * t1;
         const double t2 = fma(k2, h, -r);
-        if (__double2hiint(t2) >= 0) {
+        if (__double2hiint(t2) >= hi_eps) {
             p = fma(-5.0, (t2 * t2) * t2, p);
             const double t3 = fma(k3, h, -r);
-            if (__double2hiint(t3) >= 0) p = fma(10.0, (t3 * t3) * t3, p);
+            if (__double2hiint(t3) >= hi_eps) p = fma(10.0, (t3 * t3) * t3, p);
         }
     }
     return p;
 }
+// The tests above compare the HIGH WORD of t_k with that of eps = kPieceEps * h (positive doubles order like
+// their high words; a negative t_k has the sign bit set and compares below): a piece is entered only where
+// t_k >= eps.  A piece with 0 <= t_k < 1e-7 h would contribute (t_k/h)^3 < 1e-21 of a typical term — far
+// below the rounding of the sum — and leaving it out keeps neighbouring lanes on the same side of the
+// branch when a neighbour sits on a knot of the spline to within rounding, which on a lattice with
+// h = 2 spacings is EVERY neighbour (q = 0.5, 1, 1.5, 2, 2.5).
+constexpr double kPieceEps = 1e-7;
 constexpr double kGradC = -4.0 * kSigma;   // w'(q)/h^2 = kGradC / h^5 * dpoly(r, h)
 
 // What the density pass leaves per particle for the force pass: everything a pair needs from
@@ -133,8 +140,8 @@ constexpr int kLocalIters = 48;  // cap on the in-tile iterations of one refinem
 // one is outside as well.
 // one neighbour at distance r (0 <= r < 2.5 h): adds its terms to sw, sg
 template <bool UM>
-__device__ __forceinline__ void density_term(double r, double a1, double a2, double a3, double mj, double &sw,
-                                             double &sg, double &sgr) {
+__device__ __forceinline__ void density_term(double r, double a1, double a2, double a3, int hi_eps, double mj,
+                                             double &sw, double &sg, double &sgr) {
     const double t1 = a1 - r;
     const double c1 = (t1 * t1) * t1;
     const double r5 = 5.0 * r;
@@ -142,13 +149,13 @@ __device__ __forceinline__ void density_term(double r, double a1, double a2, dou
     double g = c1 * (a1 - r5);
     double d = c1;                                 // T1^3 - 5 T2^3 + 10 T3^3: the gradient's polynomial
     const double t2 = a2 - r;
-    if (__double2hiint(t2) >= 0) {                 // sign tests run off the FP64 pipe (see dpoly_from)
+    if (__double2hiint(t2) >= hi_eps) {            // these tests run off the FP64 pipe (see dpoly_from)
         const double c2 = -5.0 * ((t2 * t2) * t2);
         sw = fma(c2, t2, sw);
         g = fma(c2, a2 - r5, g);
         d += c2;
         const double t3 = a3 - r;
-        if (__double2hiint(t3) >= 0) {
+        if (__double2hiint(t3) >= hi_eps) {
             const double c3 = 10.0 * ((t3 * t3) * t3);
             sw = fma(c3, t3, sw);
             g = fma(c3, a3 - r5, g);
@@ -162,8 +169,8 @@ __device__ __forceinline__ void density_term(double r, double a1, double a2, dou
 template <bool UM, int DIR>
 __device__ __forceinline__ void density_side(Ctl *ctl, bool own, const double *sx, int wbase, int wn, const double *__restrict__ gx,
                                              const double *__restrict__ m, int s, int lo, int hi, double xi,
-                                             double h, double a1, double a2, double a3, double r_in, double &sw,
-                                             double &sg, double &sgr, int &c) {
+                                             double h, double a1, double a2, double a3, double r_in, int hi_eps,
+                                             double &sw, double &sg, double &sgr, int &c) {
     int k = s - wbase + DIR;
     double r;
 #pragma unroll 1
@@ -171,7 +178,7 @@ __device__ __forceinline__ void density_side(Ctl *ctl, bool own, const double *s
         r = DIR > 0 ? (sx[k] - xi) : (xi - sx[k]);
         if (!(r < r_in)) break;
         c++;
-        density_term<UM>(r, a1, a2, a3, UM ? 0.0 : __ldg(m + wbase + k), sw, sg, sgr);
+        density_term<UM>(r, a1, a2, a3, hi_eps, UM ? 0.0 : __ldg(m + wbase + k), sw, sg, sgr);
         k += DIR;
     }
     // From here on r >= r_in (x is sorted): only particles within rounding of the support edge can
@@ -190,7 +197,7 @@ __device__ __forceinline__ void density_side(Ctl *ctl, bool own, const double *s
         r = DIR > 0 ? (__ldg(gx + j) - xi) : (xi - __ldg(gx + j));
         if (r < r_in) {
             c++;
-            density_term<UM>(r, a1, a2, a3, UM ? 0.0 : __ldg(m + j), sw, sg, sgr);
+            density_term<UM>(r, a1, a2, a3, hi_eps, UM ? 0.0 : __ldg(m + j), sw, sg, sgr);
         } else if (r / h < kRadius) {
             c++;
         } else {
@@ -213,8 +220,9 @@ __device__ __forceinline__ void density_sums(Ctl *ctl, bool own, const double *s
     double sw = self, sg = UM ? self : self * __ldg(m + s);
     int c = 1;
     double grl = 0.0, grr = 0.0;
-    density_side<UM, -1>(ctl, own, sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, grl, c);
-    density_side<UM, +1>(ctl, own, sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, sw, sg, grr, c);
+    const int hi_eps = __double2hiint(kPieceEps * h);
+    density_side<UM, -1>(ctl, own, sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, hi_eps, sw, sg, grl, c);
+    density_side<UM, +1>(ctl, own, sx, wbase, wn, gx, m, s, lo, hi, xi, h, a1, a2, a3, r_in, hi_eps, sw, sg, grr, c);
     Sw = sw;
     Sg = sg;
     Sgr = grl - grr;                              // gradW carries sign(x_i - x_j): + for left neighbours
@@ -480,8 +488,10 @@ template <bool ADIA>
 struct Own {
     double x, h, rho, v, PrRho, c_ac, c_ec, P;
     unsigned idx;
+    int hi_eps;      // high word of kPieceEps * h: spline pieces below it are left out (see dpoly_from)
     __device__ __forceinline__ void set(double xi, unsigned idxi, const Rec &r, double vi, double ui, double Pstale) {
         x = xi; idx = idxi; h = r.h; rho = r.rho; v = vi;
+        hi_eps = __double2hiint(kPieceEps * r.h);
         P = ADIA ? ((kGamma - 1) * ui) * r.rho : r.rho;                 // calculators.cpp:131-137
         c_ac = ADIA ? sqrt(kGamma * Pstale / r.rho) : 1.0;              // stale stored pressure
         c_ec = ADIA ? sqrt(kGamma * P / r.rho) : 1.0;                   // fresh pressure
@@ -500,7 +510,7 @@ __device__ __forceinline__ bool pair_terms(const Own<ADIA> &o, double ar, double
                                            double uj, double mj, double &accA, double &accE) {
     const double hs = o.h + rj.h;
     const double t1j = fma(2.5, rj.h, -ar), t1b = fma(1.25, hs, -ar);
-    if ((__double2hiint(t1j) & __double2hiint(t1b)) < 0) return false;   // beyond 2.5 h_j and 2.5 hbar
+    if (max(__double2hiint(t1j), __double2hiint(t1b)) < o.hi_eps) return false;   // beyond (or on the edge of) 2.5 h_j and 2.5 hbar
     const double rs = o.rho + rj.rho;
     const double D = fma(ar, ar, 0.0025 * (hs * hs));        // r^2 + 0.01 hbar^2
     // one reciprocal serves 1/hbar, 1/D and 1/(rho_i + rho_j)
@@ -512,9 +522,9 @@ __device__ __forceinline__ bool pair_terms(const Own<ADIA> &o, double ar, double
     const double irs = t * D;
     const double ihs2 = ihs * ihs;
     // gradW(hbar) without its sign: -4 sigma / hbar^5 * poly = -128 sigma / hs^5 * poly
-    const double gb = dpoly_from(t1b, ar, hs, 0.75, 0.25) * ((32.0 * kGradC) * ((ihs2 * ihs2) * ihs));
+    const double gb = dpoly_from(t1b, ar, hs, 0.75, 0.25, o.hi_eps) * ((32.0 * kGradC) * ((ihs2 * ihs2) * ihs));
     const double PrRho_j = ADIA ? ((kGamma - 1) * uj) * rj.kap : rj.kap;
-    const double gj = dpoly_from(t1j, ar, rj.h, 1.5, 0.5) * (rj.c5 * PrRho_j);
+    const double gj = dpoly_from(t1j, ar, rj.h, 1.5, 0.5, o.hi_eps) * (rj.c5 * PrRho_j);
     const double v_ij = o.v - vj;
     const double dot = v_ij * (dir * ar);
     // artificial viscosity (calculators.cpp:148-172): alpha = 1, beta = 2, eta^2 = 0.01 hbar^2
