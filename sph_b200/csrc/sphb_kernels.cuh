@@ -553,6 +553,7 @@ struct ForceSmem {
     double vB[kTile + 2 * kFHalo], uB[kTile + 2 * kFHalo];
     unsigned idx[kTile + 2 * kFHalo];
     double gsum[kTile], pst[kTile];      // own particles: gradient sum of the density pass, stored pressure
+    unsigned hw[kTile / 32];             // per warp: largest smoothing length it staged (float bits, rounded up)
 };
 
 template <bool VOL>
@@ -571,8 +572,8 @@ __device__ __forceinline__ bool sees_new_state(unsigned idxj, unsigned idxi) {
 // and du/dt with the opposite signs.  `jend` receives the farthest slot within reach.
 template <int SEL, bool ADIA, bool UM, bool FIRST, int DIR>
 __device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &S, const Own<ADIA> &o, int ks,
-                                           int wbase, int wn, int lo, int hi, double reach, double &a_sum,
-                                           double &e_sum, int &npairs, int &jend) {
+                                           int wbase, int wn, int lo, int hi, double reach_win,
+                                           double &a_sum, double &e_sum, int &npairs, int &jend) {
     const double *sx = S.x + 1;
     const double dir = DIR > 0 ? -1.0 : 1.0;      // sign of x_i - x_j
     double accA = 0.0, accE = 0.0;
@@ -580,7 +581,7 @@ __device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &
 #pragma unroll 1
     while (true) {
         const double ar = DIR > 0 ? (sx[k] - o.x) : (o.x - sx[k]);
-        if (!(ar < reach)) break;                 // also the +-INF sentinels
+        if (!(ar < reach_win)) break;             // also the +-INF sentinels
         const bool useA = sees_new_state<SEL>(S.idx[k], o.idx);
         const int sel = useA ? 0 : 1;
         const double2 hc = S.hc[sel][k], rk = S.rk[sel][k];
@@ -592,9 +593,16 @@ __device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &
         if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
         k += DIR;
     }
+    // Inside the staged window no particle has a larger h than reach_win / 2.5, so whatever lies beyond the
+    // point where the scan stopped cannot interact.  BEYOND the window only the global bound is known: if it
+    // reaches past the outermost staged particle, go on from there in global memory (rare: it takes an h
+    // several times the local one, or more than kFHalo neighbours on one side).
     int j = wbase + k;                            // first particle not handled above
-    if ((k < 0 || k >= wn) && j >= lo && j < hi) {
-        // rare: the reach extends beyond the staged halo — continue in global memory
+    const double dist_end = DIR > 0 ? (sx[wn - 1] - o.x) : (o.x - sx[0]);
+    // (the global bound is re-read here rather than kept in registers through the loop above)
+    const double reach = kRadius * __longlong_as_double(*((volatile long long *)&A.ctl->hmax_bits));
+    if (dist_end < reach) {
+        j = DIR > 0 ? wbase + wn : wbase - 1;
 #pragma unroll 1
         for (; j >= lo && j < hi; j += DIR) {
             const double xj = __ldg(A.F.x + j);
@@ -656,12 +664,14 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
     const int wn = min(t0 + kTile + kFHalo, hi) - wbase;
     double *sx = S.x + 1;
     __syncthreads();                                   // previous tile's readers are done
+    double hstaged = 0.0;
     for (int k = threadIdx.x; k < wn; k += kTile) {
         const int j = wbase + k;
         sx[k] = A.F.x[j];
         S.idx[k] = A.F.idx[j];
         {
             const Rec2 r2 = A.F.rec[j];
+            hstaged = fmax(hstaged, fmax(r2.A.h, r2.B.h));
             S.hc[0][k] = make_double2(r2.A.h, r2.A.c5); S.rk[0][k] = make_double2(r2.A.rho, r2.A.kap);
             S.hc[1][k] = make_double2(r2.B.h, r2.B.c5); S.rk[1][k] = make_double2(r2.B.rho, r2.B.kap);
         }
@@ -673,8 +683,17 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
         S.gsum[threadIdx.x] = A.F.gsum[t0 + threadIdx.x];
         S.pst[threadIdx.x] = A.Pstale[t0 + threadIdx.x];
     }
+    {
+        const unsigned wm = __reduce_max_sync(0xffffffffu, __float_as_uint(__double2float_ru(hstaged)));
+        if ((threadIdx.x & 31) == 0) S.hw[threadIdx.x >> 5] = wm;
+    }
     if (threadIdx.x == 0) { sx[-1] = -INFINITY; sx[wn] = INFINITY; }
     __syncthreads();
+    // the scan bound inside the staged window: 2.5 x the largest h staged (rounded up), never above the global one
+    unsigned hwb = S.hw[0];
+#pragma unroll
+    for (int w = 1; w < kTile / 32; w++) hwb = max(hwb, S.hw[w]);
+    const double reach_win = fmin(kRadius * Hb, kRadius * (double)__uint_as_float(hwb));
 
     const int s = t0 + threadIdx.x;
     bool changed = false;
@@ -693,12 +712,11 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
                 ro.h = S.hc[0][ks2].x; ro.c5 = S.hc[0][ks2].y; ro.rho = S.rk[0][ks2].x; ro.kap = S.rk[0][ks2].y;
                 o.set(sx[ks2], S.idx[ks2], ro, vi, ui, S.pst[threadIdx.x]);
             }
-            const double reach2 = kRadius * Hb;
             double a_sum = 0.0, e_sum = 0.0;
             int jmin = s, jmax = s;
             npairs = 1;   // self: its energy term is evaluated by the reference too (and is exactly 0)
-            force_side<SEL, ADIA, UM, true, -1>(A, S, o, ks2, wbase, wn, lo, hi, reach2, a_sum, e_sum, npairs, jmin);
-            force_side<SEL, ADIA, UM, true, +1>(A, S, o, ks2, wbase, wn, lo, hi, reach2, a_sum, e_sum, npairs, jmax);
+            force_side<SEL, ADIA, UM, true, -1>(A, S, o, ks2, wbase, wn, lo, hi, reach_win, a_sum, e_sum, npairs, jmin);
+            force_side<SEL, ADIA, UM, true, +1>(A, S, o, ks2, wbase, wn, lo, hi, reach_win, a_sum, e_sum, npairs, jmax);
             if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
             a_sum = fma(-o.PrRho, S.gsum[threadIdx.x], a_sum);   // - P_i/(rho_i^2 om_i) sum_j m_j gradW_ij(h_i)
             if (!A.kick) {
@@ -722,7 +740,6 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
         // inside a tile then costs CTA barriers instead of grid-wide sweeps.
         const bool active = s < tend;
         const int ks = s - wbase;
-        const double reach = kRadius * Hb;
         bool local_cap = false;
         Own<ADIA> o;
         double vi = 0.0, ui = 0.0, gsum = 0.0, vscale = 1.0;
@@ -740,8 +757,8 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
             bool moved = false;
             if (active) {
                 a_sum = 0.0; e_sum = 0.0;
-                force_side<SEL, ADIA, UM, false, -1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmin);
-                force_side<SEL, ADIA, UM, false, +1>(A, S, o, ks, wbase, wn, lo, hi, reach, a_sum, e_sum, npairs, jmax);
+                force_side<SEL, ADIA, UM, false, -1>(A, S, o, ks, wbase, wn, lo, hi, reach_win, a_sum, e_sum, npairs, jmin);
+                force_side<SEL, ADIA, UM, false, +1>(A, S, o, ks, wbase, wn, lo, hi, reach_win, a_sum, e_sum, npairs, jmax);
                 if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
                 a_sum = fma(-o.PrRho, gsum, a_sum);
                 vf = __dadd_rn(vi, __dmul_rn(a_sum, A.half_dt));
