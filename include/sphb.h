@@ -74,7 +74,7 @@ typedef struct sphb_counters {
     long long steps;            /* steps taken by sphb_step since creation */
     long long sweeps_total;     /* force sweeps over all steps (>= steps) */
     int sweeps_last;            /* force sweeps of the most recent step */
-    long long sorts;            /* radix sorts performed */
+    long long sorts;            /* x-order repairs performed: radix sorts + cheap transposition repairs */
     long long fallbacks;        /* bisection fallbacks (smoothing_length.cpp:246-254) */
     long long newton_hist[12];  /* most recent density pass: particles by Newton iteration count */
     int nbr_min, nbr_max;       /* most recent density pass: neighbours with |dx|/h < 2.5, incl. self */

@@ -69,7 +69,8 @@ struct sphb_handle {
     bool uniform_mass = true;
     double m0 = 0.0;
     bool have_counts = false;
-    long long steps = 0, sweeps_total = 0, sorts = 0;
+    long long steps = 0, sweeps_total = 0, sorts = 0, swap_repairs = 0;
+    int resorts_this_step = 0;
     unsigned long long fallbacks_committed = 0;   // bisection fallbacks of finished steps (a repeated attempt restarts from it)
     int sweeps_last = 0;
     int epoch = 8;
@@ -84,6 +85,8 @@ struct sphb_handle {
 };
 
 namespace {
+
+constexpr int kSwapPasses = 4;   // odd-even transposition rounds of the cheap order repair
 
 #define CK(call)                                                                              \
     do {                                                                                      \
@@ -371,6 +374,7 @@ SweepArgs sweep_args(sphb_handle *H) {
 // of the step.  In the rare step where it is set, the alive block is radix-sorted and the phases
 // after the drift run again; nothing of the previous state has been overwritten by then.
 int step_begin(sphb_handle *H) {   // kick-drift + order flag, wall ghosts
+    H->resorts_this_step = 0;
     if (H->epoch > 0x7fff0000 - 4 * H->opt.max_sweeps) {   // stamp wrap-around
         CK(cudaMemsetAsync(H->dirty, 0, sizeof(int) * (size_t)nblk(H->cap_alive, kTile), H->stream));
         H->epoch = 8;
@@ -391,11 +395,26 @@ int step_begin(sphb_handle *H) {   // kick-drift + order flag, wall ghosts
     return SPHB_OK;
 }
 
-// after an attempt found the order flag set: sort, re-select the ghost candidates, rebuild the ghosts
+// After an attempt found the order flag set: restore the x order, re-select the ghost candidates, rebuild
+// the ghosts.  The first repair of a step is a few odd-even transposition steps (a drift seldom does more
+// than swap a handful of neighbours); if the next attempt still finds the flag set, the radix sort runs.
 int step_resort(sphb_handle *H) {
     CK(cudaMemcpyAsync(&H->d_ctl->fallbacks, &H->fallbacks_committed, sizeof(unsigned long long),
                        cudaMemcpyHostToDevice, H->stream));
-    TRY(sort_alive(H, false));
+    if (H->resorts_this_step++ == 0 && H->na > 1) {
+        SwapArgs W;
+        W.x = H->x; W.vh = H->vh; W.uh = H->uh; W.a = H->a; W.du = H->du; W.h = H->h; W.rho = H->rho; W.P = H->P;
+        W.m = H->m; W.idx = H->idx; W.pad = H->pad; W.na = H->na;
+        const int grid = nblk((H->na + 1) / 2, 256);
+        for (int pass = 0; pass < 2 * kSwapPasses; pass++) {
+            k_swap_inversions<<<grid, 256, 0, H->stream>>>(W, pass & 1);
+            H->launches++;
+        }
+        CK(cudaGetLastError());
+        H->swap_repairs++;
+    } else {
+        TRY(sort_alive(H, false));
+    }
     TRY(launch_begin(H, 1));
     TRY(launch_kick(H, 0));
     TRY(launch_ghost_build(H, 1, 0, H->vh, H->uh, H->vh, H->uh, true));
@@ -484,8 +503,8 @@ int step_once(sphb_handle *H) {
         TRY(step_refine(H));
         int err, unsorted, changed;
         TRY(step_flags(H, &err, &unsorted, &changed));
-        if (unsorted && attempt == 0) {
-            // whatever the kernels complained about came from the broken order: forget it, sort, redo
+        if (unsorted && attempt < 2) {
+            // whatever the kernels complained about came from the broken order: forget it, repair, redo
             CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, 2 * sizeof(int), H->stream));
             TRY(step_resort(H));
             continue;
@@ -1246,13 +1265,14 @@ int sphb_slab_step(sphb_handle *H, int nsteps) {
         int rounds = 0;
         TRY(native_attempt(H, &rounds));
         TRY(native_flags(H));
-        if (H->h_flags[1]) {
-            // some rank's drift swapped two neighbours: those ranks sort, everybody repeats the attempt
+        for (int repair = 0; repair < 2 && H->h_flags[1]; repair++) {
+            // some rank's drift swapped neighbours: those ranks repair their order (transposition steps first,
+            // the radix sort if that was not enough), everybody repeats the attempt
             TRY(sphb_slab_resort(H));
             TRY(native_attempt(H, &rounds));
             TRY(native_flags(H));
-            if (H->h_flags[1]) { H->err = "x-order still broken after the sort (a particle crossed a slab edge)"; return SPHB_ERR_UNSORTED; }
         }
+        if (H->h_flags[1]) { H->err = "x-order still broken after the sort"; return SPHB_ERR_UNSORTED; }
         while (H->h_flags[2] && !H->h_flags[0]) {
             if (rounds > H->opt.max_sweeps) { H->err = "x-slab ordered sweep did not settle"; return SPHB_ERR_NOT_CONVERGED; }
             TRY(step_refine(H));
@@ -1283,7 +1303,7 @@ int sphb_get_counters(sphb_handle *H, sphb_counters *out) {
     out->steps = H->steps;
     out->sweeps_total = H->sweeps_total;
     out->sweeps_last = H->sweeps_last;
-    out->sorts = H->sorts;
+    out->sorts = H->sorts + H->swap_repairs;   // radix sorts + transposition repairs
     out->fallbacks = (long long)H->h_ctl->fallbacks;
     out->h_max = 0.0;
     { long long b = (long long)H->h_ctl->hmax_bits; memcpy(&out->h_max, &b, sizeof(double)); }

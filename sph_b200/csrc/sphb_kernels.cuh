@@ -1307,6 +1307,27 @@ __global__ void __launch_bounds__(1024) k_slab_unpack2(SlabArgs A, int what, con
 __global__ void k_slab_flags(Ctl *ctl, int hl, int hr) { ctl->halo_left = hl; ctl->halo_right = hr; }
 
 // ------------------------------------------------------------------------------------
+// A drift rarely breaks the x order by more than a few adjacent swaps.  One odd-even transposition
+// step over the alive block: pairs (s, s+1) with s = pad + 2t + parity that are out of order swap every
+// per-particle array that is live between the drift and the density pass.  A few steps of this repair
+// such a step for the cost of reading x; the radix sort remains for what they cannot repair.
+struct SwapArgs {
+    double *x, *vh, *uh, *a, *du, *h, *rho, *P, *m;
+    unsigned *idx;
+    int pad, na;
+};
+__global__ void k_swap_inversions(SwapArgs A, int parity) {
+    const int q = 2 * (blockIdx.x * blockDim.x + threadIdx.x) + parity;
+    if (q + 1 >= A.na) return;
+    const int s = A.pad + q;
+    if (!(A.x[s] > A.x[s + 1])) return;
+    double *arrs[9] = {A.x, A.vh, A.uh, A.a, A.du, A.h, A.rho, A.P, A.m};
+#pragma unroll
+    for (int k = 0; k < 9; k++) { const double t = arrs[k][s]; arrs[k][s] = arrs[k][s + 1]; arrs[k][s + 1] = t; }
+    const unsigned ti = A.idx[s]; A.idx[s] = A.idx[s + 1]; A.idx[s + 1] = ti;
+}
+
+// ------------------------------------------------------------------------------------
 // sort support
 __global__ void k_iota(int *p, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -269,14 +269,17 @@ class SlabSimulation:
             self._all("step_begin")
             rounds = self._attempt()
             (err, unsorted, changed), mine = self._flags()
-            if unsorted:
-                # some rank's drift swapped two neighbours: those ranks sort, everybody repeats the
-                # attempt (nothing of the previous state has been overwritten)
+            for _repair in range(2):
+                if not unsorted:
+                    break
+                # some rank's drift swapped neighbours: those ranks repair their order (a few transposition
+                # steps first, the radix sort if that was not enough), everybody repeats the attempt
+                # (nothing of the previous state has been overwritten)
                 self._all("resort")
                 rounds = self._attempt()
                 (err, unsorted, changed), mine = self._flags()
-                if unsorted:
-                    raise SphbError(11, "x-order still broken after the sort (a particle crossed a slab edge: rebalance)")
+            if unsorted:
+                raise SphbError(11, "x-order still broken after the sort")
             while changed and not err:
                 if rounds > self.max_rounds:
                     raise SphbError(10, "x-slab ordered sweep did not settle in %d rounds" % self.max_rounds)
