@@ -304,6 +304,9 @@ def run_ours(args, name, n, pc, varh):
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "traffic_source": "profiles/traffic_r01.json: ncu dram__bytes_read+write per launch at N = 64 Mi (--set full), scaled per particle",
                 "peak_source": peak_src, "bytes_per_particle": dom[2], "launch_ms": dom[1],
+                "note": "algorithmic bytes count every neighbour read (SURVEY 8d) although tiles serve them from shared memory; "
+                        "ncu: both hot kernels move their compulsory bytes once and are limited by the half-rate FP64 pipe and "
+                        "instruction issue (profiles/r01_summary.md)",
                 "step_b_ns_bytes_per_particle": b_ns,
                 "step_frac_b_ns": value / world * b_ns / 1e9 / peak,
                 "step_frac_compulsory_244B": value / world * (244.0 if varh else 156.0) / 1e9 / peak,

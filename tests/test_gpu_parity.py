@@ -287,6 +287,30 @@ def test_against_oracle_at_one_million():
     sim.close()
 
 
+def test_developed_flow_long_run():
+    """N = 2001 to t = 0.5 (2000 steps): smoothing lengths end up a factor ~8 apart, particles have swapped
+    places, the ghost sets have changed — the paths a short run from the lattice never takes (order repair,
+    tiles whose reach exceeds their staged halo, global continuation of the scans).  Rounding differences
+    have 2000 steps to grow here, hence the looser limit; n_ghost must still be equal at the end."""
+    n = 2001
+    kw = dict(n_part=n, mass=4.0 / (n - 1), pressure_calc=1, limit=2.0, v_0=1.0, h_factor=2.0,
+              t_i=0.005 * 100 / (n - 1), variable_h=True, constant_h=0.2)
+    o = _oracle(kw)
+    sim = _sim(kw)
+    sim.init_lattice()
+    o.step(2000)
+    sim.step(2000)
+    f, typ, ng = sim.fields()
+    ref = o.fields()
+    assert ng == o.n_ghost
+    h = ref[:n, COLS["h"]]
+    assert h.max() / h.min() > 5 and (np.diff(ref[:n, COLS["pos"]]) < 0).any()
+    _compare(f, ref, n, True, "N=2001 step 2000", tol=1e-7, cols=["pos", "vel", "h", "u", "density", "pressure"])
+    c = sim.counters()
+    assert c.sorts >= 1 and c.fallbacks == 0
+    sim.close()
+
+
 def test_large_n_properties():
     """N = 1M (BASELINE config-2 size), adiabatic variable h: properties that need no oracle.
     The lattice is mirror-symmetric and both streams are uniform away from the centre and
