@@ -304,6 +304,8 @@ def run_ours(args, name, n, pc, varh):
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "traffic_source": "profiles/traffic_r01.json: ncu dram__bytes_read+write per launch at N = 64 Mi (--set full), scaled per particle",
                 "peak_source": peak_src, "bytes_per_particle": dom[2], "launch_ms": dom[1],
+                "compulsory_bytes_per_particle": (148.0 if dom[0] != "density" else 116.0),
+                "frac_compulsory": (n_local * (148.0 if dom[0] != "density" else 116.0) / (dom[1] * 1e-3) / 1e9 / peak) if dom[1] > 0 else None,
                 "note": "algorithmic bytes count every neighbour read (SURVEY 8d) although tiles serve them from shared memory; "
                         "ncu: both hot kernels move their compulsory bytes once and are limited by the half-rate FP64 pipe and "
                         "instruction issue (profiles/r01_summary.md)",
