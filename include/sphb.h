@@ -160,6 +160,9 @@ int sphb_kick_drift(sphb_handle *h);
 int sphb_step(sphb_handle *h, int nsteps);
 
 int sphb_get_counters(sphb_handle *h, sphb_counters *out);
+/* No counterpart in the reference (its author lists conservation checks as missing, readme.md:23): totals over
+ * the alive particles of this handle, out4 = { sum m, sum m v, sum m v^2 / 2, sum m u }, summed in a fixed order. */
+int sphb_diagnostics(sphb_handle *h, double *out4);
 int sphb_get_config(const sphb_handle *h, sphb_config *out);
 
 /* Per-phase device time, CUDA events on the handle's stream.  Phases:

@@ -143,6 +143,7 @@ def load_library():
     L.sphb_kick_drift.argtypes = [p]
     L.sphb_step.argtypes = [p, i]
     L.sphb_get_counters.argtypes = [p, C.POINTER(SphbCounters)]
+    L.sphb_diagnostics.argtypes = [p, C.POINTER(d)]
     L.sphb_get_config.argtypes = [p, C.POINTER(SphbConfig)]
     L.sphb_set_profiling.argtypes = [p, i]
     L.sphb_get_phase_times.argtypes = [p, C.POINTER(d), C.POINTER(C.c_longlong), i]
@@ -300,6 +301,22 @@ class Simulation:
         return Counters(c.n_alive, c.n_ghost, c.steps, c.sweeps_total, c.sweeps_last, c.sorts,
                         c.fallbacks, list(c.newton_hist), c.nbr_min, c.nbr_max, c.nbr_mean, c.h_max,
                         c.launches, c.force_pairs_mean, c.density_scans_mean, c.refine_tiles, c.refine_tile_evals)
+
+    def diagnostics(self):
+        """{mass, momentum, kinetic, thermal} totals over the alive particles (sphb_diagnostics)."""
+        out = (C.c_double * 4)()
+        self._check(self.L.sphb_diagnostics(self.h, out))
+        return dict(mass=out[0], momentum=out[1], kinetic=out[2], thermal=out[3])
+
+    # ---- checkpoint / restart: the nine fields of every record, in array order, ARE the complete state
+    def save(self, path):
+        rec, ng = self.download()
+        np.savez(path, records=rec, n_ghost=ng)
+
+    def load(self, path):
+        z = np.load(path)
+        rec = np.ascontiguousarray(z["records"])
+        self.upload(rec, int(z["n_ghost"]))
 
     def set_profiling(self, on=True):
         self._check(self.L.sphb_set_profiling(self.h, int(on)))

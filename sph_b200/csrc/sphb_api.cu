@@ -1293,6 +1293,22 @@ int sphb_slab_step(sphb_handle *H, int nsteps) {
 
 int sphb_slab_rounds_last(const sphb_handle *H) { return H ? H->rounds_last : -1; }
 
+int sphb_diagnostics(sphb_handle *H, double *out4) {
+    if (!H || !out4) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    // scratch: the gather temporary is free between steps (4 * kDiagBlocks + 4 doubles are needed)
+    if ((size_t)H->total < (size_t)4 * kDiagBlocks + 4) { H->err = "handle too small for the diagnostics scratch"; return SPHB_ERR_CAPACITY; }
+    double *partial = H->tmp, *res = H->tmp + 4 * kDiagBlocks;
+    const int nb = std::max(1, std::min(kDiagBlocks, nblk(H->na, 256)));
+    k_diag_partial<<<nb, 256, 0, H->stream>>>(H->m, H->v, H->u, H->pad, H->na, partial);
+    k_diag_final<<<1, 256, 0, H->stream>>>(partial, nb, res);
+    H->launches += 2;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out4, res, 4 * sizeof(double), cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaStreamSynchronize(H->stream));
+    return SPHB_OK;
+}
+
 int sphb_get_counters(sphb_handle *H, sphb_counters *out) {
     if (!H || !out) return SPHB_ERR_INVALID;
     CK(cudaSetDevice(H->device));

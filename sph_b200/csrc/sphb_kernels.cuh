@@ -1307,6 +1307,44 @@ __global__ void __launch_bounds__(1024) k_slab_unpack2(SlabArgs A, int what, con
 __global__ void k_slab_flags(Ctl *ctl, int hl, int hr) { ctl->halo_left = hl; ctl->halo_right = hr; }
 
 // ------------------------------------------------------------------------------------
+// Conservation diagnostics over the alive particles (the checks the reference's author wished for,
+// readme.md:23): sum m, sum m v, sum m v^2 / 2, sum m u.  Two stages with a fixed summation tree, so the
+// numbers are reproducible run to run: CTA partials, then one CTA adds the partials in order.
+constexpr int kDiagBlocks = 1024;
+__global__ void __launch_bounds__(256) k_diag_partial(const double *m, const double *v, const double *u, int pad, int na,
+                                                      double *partial) {
+    double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < na; i += gridDim.x * blockDim.x) {
+        const double mi = m[pad + i], vi = v[pad + i], ui = u[pad + i];
+        s0 += mi; s1 = fma(mi, vi, s1); s2 = fma(0.5 * mi, vi * vi, s2); s3 = fma(mi, ui, s3);
+    }
+    __shared__ double sh[4][256];
+    sh[0][threadIdx.x] = s0; sh[1][threadIdx.x] = s1; sh[2][threadIdx.x] = s2; sh[3][threadIdx.x] = s3;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o)
+            for (int q = 0; q < 4; q++) sh[q][threadIdx.x] += sh[q][threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x < 4) partial[threadIdx.x * kDiagBlocks + blockIdx.x] = sh[threadIdx.x][0];
+}
+__global__ void __launch_bounds__(256) k_diag_final(const double *partial, int nblocks, double *out) {
+    __shared__ double sh[4][256];
+    for (int q = 0; q < 4; q++) {
+        double s = 0;
+        for (int b = threadIdx.x; b < nblocks; b += 256) s += partial[q * kDiagBlocks + b];
+        sh[q][threadIdx.x] = s;
+    }
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o)
+            for (int q = 0; q < 4; q++) sh[q][threadIdx.x] += sh[q][threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x < 4) out[threadIdx.x] = sh[threadIdx.x][0];
+}
+
+// ------------------------------------------------------------------------------------
 // A drift rarely breaks the x order by more than a few adjacent swaps.  One odd-even transposition
 // step over the alive block: pairs (s, s+1) with s = pad + 2t + parity that are out of order swap every
 // per-particle array that is live between the drift and the density pass.  A few steps of this repair
