@@ -570,10 +570,14 @@ __device__ __forceinline__ bool sees_new_state(unsigned idxj, unsigned idxi) {
 // first, then (rarely) global memory.  gradW carries sign(x_i - x_j) (calculators.cpp:17-27): the
 // unsigned sums of this side enter a with -DIR... i.e. a -= accA on the left, a += accA on the right,
 // and du/dt with the opposite signs.  `jend` receives the farthest slot within reach.
-template <int SEL, bool ADIA, bool UM, bool FIRST, int DIR>
+// SPLIT (refinement): a_sum / e_sum receive this side's unsigned sums instead of being merged, and `dyn` tells
+// whether the side holds a neighbour whose value can change while the tile iterates (seen in its new state and
+// inside the tile [dyn_lo, dyn_hi) of the staged window): a side without one need not be recomputed.
+template <int SEL, bool ADIA, bool UM, bool FIRST, int DIR, bool SPLIT = false>
 __device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &S, const Own<ADIA> &o, int ks,
                                            int wbase, int wn, int lo, int hi, double reach_win,
-                                           double &a_sum, double &e_sum, int &npairs, int &jend) {
+                                           double &a_sum, double &e_sum, int &npairs, int &jend,
+                                           int dyn_lo = 0, int dyn_hi = 0, bool *dyn = nullptr) {
     const double *sx = S.x + 1;
     const double dir = DIR > 0 ? -1.0 : 1.0;      // sign of x_i - x_j
     double accA = 0.0, accE = 0.0;
@@ -590,7 +594,10 @@ __device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &
         const double vj = (useA && !FIRST) ? S.vA[k] : S.vB[k];
         const double uj = (useA && !FIRST) ? S.uA[k] : S.uB[k];
         const double mj = UM ? 0.0 : __ldg(A.F.m + wbase + k);
-        if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
+        if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) {
+            npairs++;
+            if (SPLIT && useA && k >= dyn_lo && k < dyn_hi) *dyn = true;
+        }
         k += DIR;
     }
     // Inside the staged window no particle has a larger h than reach_win / 2.5, so whatever lies beyond the
@@ -618,8 +625,13 @@ __device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &
     }
     if ((j < lo || j >= hi) && (DIR < 0 ? A.ctl->halo_left : A.ctl->halo_right)) raise(A.ctl, E_HALO, wbase + ks);
     jend = j - DIR;
-    a_sum = DIR > 0 ? (a_sum + accA) : (a_sum - accA);
-    e_sum = DIR > 0 ? (e_sum - accE) : (e_sum + accE);
+    if (SPLIT) {
+        a_sum = accA;
+        e_sum = accE;
+    } else {
+        a_sum = DIR > 0 ? (a_sum + accA) : (a_sum - accA);
+        e_sum = DIR > 0 ? (e_sum - accE) : (e_sum + accE);
+    }
 }
 
 // Every tile holding a particle within reach of a changed one must be looked at again next sweep
@@ -752,13 +764,25 @@ __device__ __forceinline__ void force_tile(const SweepArgs &A, int tile, int lo,
         }
         double a_sum = 0.0, e_sum = 0.0, vf = 0.0, uf = 0.0;
         int jmin = s, jmax = s;
+        // Per side: its unsigned sums and whether anything in it can move while this tile iterates.  With the
+        // array order equal to the x order (the usual case) the right-hand neighbours all have a higher index,
+        // are seen in their old state, and that half of the work is done once per sweep.
+        double La = 0.0, Le = 0.0, Ra = 0.0, Re = 0.0;
+        bool dynL = false, dynR = false;
+        const int dyn_lo = t0 - wbase, dyn_hi = tend - wbase;
 #pragma unroll 1
         for (int it = 0;; it++) {
             bool moved = false;
             if (active) {
-                a_sum = 0.0; e_sum = 0.0;
-                force_side<SEL, ADIA, UM, false, -1>(A, S, o, ks, wbase, wn, lo, hi, reach_win, a_sum, e_sum, npairs, jmin);
-                force_side<SEL, ADIA, UM, false, +1>(A, S, o, ks, wbase, wn, lo, hi, reach_win, a_sum, e_sum, npairs, jmax);
+                if (it == 0 || dynL)
+                    force_side<SEL, ADIA, UM, false, -1, true>(A, S, o, ks, wbase, wn, lo, hi, reach_win, La, Le, npairs, jmin,
+                                                               dyn_lo, dyn_hi, &dynL);
+                if (it == 0 || dynR)
+                    force_side<SEL, ADIA, UM, false, +1, true>(A, S, o, ks, wbase, wn, lo, hi, reach_win, Ra, Re, npairs, jmax,
+                                                               dyn_lo, dyn_hi, &dynR);
+                // merged exactly as the first sweep merges them: (0 - left) + right, (0 + left) - right
+                a_sum = (0.0 - La) + Ra;
+                e_sum = (0.0 + Le) - Re;
                 if (UM) { a_sum *= A.m0; e_sum *= A.m0; }
                 a_sum = fma(-o.PrRho, gsum, a_sum);
                 vf = __dadd_rn(vi, __dmul_rn(a_sum, A.half_dt));
