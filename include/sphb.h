@@ -200,7 +200,8 @@ int sphb_slab_step_begin(sphb_handle *h);   /* kick-drift, order check (+ sort),
 int sphb_slab_density(sphb_handle *h);      /* density + root-find + omega + records of own particles */
 int sphb_slab_force_first(sphb_handle *h);  /* first force sweep + second kick */
 int sphb_slab_refine(sphb_handle *h);       /* ordered-sweep refinement until the local work list is empty */
-int sphb_slab_poll(sphb_handle *h, int *flags3);  /* {device error code, x-order broken, halo iterate changed} */
+int sphb_slab_poll(sphb_handle *h, int *flags4);  /* {device error code, x-order broken, halo iterate changed, h max as float bits} */
+int sphb_slab_check_halo(sphb_handle *h, int hmax_float_bits);   /* with MAX over ranks of flags4[3]: do my halos cover it? */
 int sphb_slab_resort(sphb_handle *h);       /* after a poll saw 'order broken' on some rank */
 int sphb_slab_raise(sphb_handle *h);        /* the polled error code as status + message */
 int sphb_slab_step_end(sphb_handle *h);

@@ -638,6 +638,8 @@ __global__ void k_flags(const Ctl *ctl, int *flags) {
     flags[0] = ctl->err_code;
     flags[1] = ctl->unsorted;
     flags[2] = ctl->halo_changed;
+    // the largest smoothing length this rank has seen, rounded up to float: positive floats order like ints
+    flags[3] = __float_as_int(__double2float_ru(__longlong_as_double((long long)ctl->hmax_bits)));
 }
 
 // pack both edges (one launch), one grouped send/recv with the neighbours, unpack both pads (one launch)
@@ -706,12 +708,28 @@ int native_attempt(sphb_handle *H, int *rounds) {
     return SPHB_OK;
 }
 
-int native_flags(sphb_handle *H) {   // -> H->h_flags[0..2] = MAX over ranks; H->h_ctl = my control block
+// The support of the largest smoothing length ANYWHERE in the run must fit inside this rank's halos: a wider one
+// could reach across a halo without either rank seeing the pair.  hmax_float_bits = MAX over ranks.
+int check_halo_width(sphb_handle *H, int hmax_float_bits) {
+    float hf;
+    memcpy(&hf, &hmax_float_bits, sizeof hf);
+    const double need = kRadius * (double)hf;
+    const double have = std::min(H->h_ctl->halo_thick[0], H->h_ctl->halo_thick[1]);
+    if (need > have) {
+        char b[256];
+        snprintf(b, sizeof b, "x-slab halo (%.6g wide) thinner than the widest kernel support in the run (%.6g): raise halo_count", have, need);
+        H->err = b;
+        return SPHB_ERR_HALO;
+    }
+    return SPHB_OK;
+}
+
+int native_flags(sphb_handle *H) {   // -> H->h_flags[0..3] = MAX over ranks; H->h_ctl = my control block
     k_flags<<<1, 1, 0, H->stream>>>(H->d_ctl, H->d_flags);
     H->launches++;
     CK(cudaGetLastError());
-    NK(g_nccl.AllReduce(H->d_flags, H->d_flags, 3, ncclInt32, ncclMax, H->comm, H->stream));
-    CK(cudaMemcpyAsync(H->h_flags, H->d_flags, 3 * sizeof(int), cudaMemcpyDeviceToHost, H->stream));
+    NK(g_nccl.AllReduce(H->d_flags, H->d_flags, 4, ncclInt32, ncclMax, H->comm, H->stream));
+    CK(cudaMemcpyAsync(H->h_flags, H->d_flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, H->stream));
     CK(cudaMemcpyAsync(H->h_ctl, H->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, H->stream));
     CK(cudaStreamSynchronize(H->stream));
     return SPHB_OK;
@@ -1167,12 +1185,24 @@ int sphb_slab_refine(sphb_handle *H) {
 }
 // The flags of the attempt in flight (the one host synchronisation of a slab step):
 //   flags[0] error code raised on the device (0 = none), flags[1] x-order broken by the drift,
-//   flags[2] the last ITERATE unpack differed from the copy held here (sweep not known finished).
+//   flags[2] the last ITERATE unpack differed from the copy held here (sweep not known finished),
+//   flags[3] the largest smoothing length seen here, as the bits of a float rounded up (orders like an int).
 // Nothing is raised here: the ranks first agree (MAX over ranks) on what to do.
 int sphb_slab_poll(sphb_handle *H, int *flags) {
     if (!H || !flags) return SPHB_ERR_INVALID;
     CK(cudaSetDevice(H->device));
-    return step_flags(H, &flags[0], &flags[1], &flags[2]);
+    TRY(step_flags(H, &flags[0], &flags[1], &flags[2]));
+    double hm;
+    { long long b = (long long)H->h_ctl->hmax_bits; memcpy(&hm, &b, sizeof hm); }
+    float up = (float)hm;
+    if ((double)up < hm) up = __builtin_nextafterf(up, __builtin_inff());   // round up
+    memcpy(&flags[3], &up, sizeof up);
+    return SPHB_OK;
+}
+// after the ranks agreed on MAX(flags): does the widest kernel support of the run fit inside my halos?
+int sphb_slab_check_halo(sphb_handle *H, int hmax_float_bits) {
+    if (!H) return SPHB_ERR_INVALID;
+    return check_halo_width(H, hmax_float_bits);
 }
 // some rank's order flag was set: sort (if mine was), forget the attempt's errors, rebuild the ghosts
 int sphb_slab_resort(sphb_handle *H) {
@@ -1228,8 +1258,8 @@ int sphb_slab_comm_init(sphb_handle *H, const void *unique_id128) {
             TRY(dalloc(H, &H->msg_send[what][k], n));
             TRY(dalloc(H, &H->msg_recv[what][k], n));
         }
-    TRY(dalloc(H, &H->d_flags, 4));
-    CK(cudaMallocHost((void **)&H->h_flags, 4 * sizeof(int)));
+    TRY(dalloc(H, &H->d_flags, 8));
+    CK(cudaMallocHost((void **)&H->h_flags, 8 * sizeof(int)));
     CK(cudaStreamCreateWithFlags(&H->comm_stream, cudaStreamNonBlocking));
     for (cudaEvent_t *e : {&H->ev_kick, &H->ev_base, &H->ev_edge, &H->ev_rec})
         CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
@@ -1285,6 +1315,7 @@ int sphb_slab_step(sphb_handle *H, int nsteps) {
             H->err = "a neighbouring slab reported a device error";
             return H->h_flags[0];
         }
+        TRY(check_halo_width(H, H->h_flags[3]));
         H->rounds_last = rounds;
         TRY(step_finish(H));
     }

@@ -61,6 +61,7 @@ struct Ctl {
     int halo_left, halo_right;     // the pad on that side holds another slab's particles, not wall ghosts
     int halo_changed;              // an incoming halo iterate differed from the copy held here
     int migrated;                  // particles that changed slab in the current attempt
+    double halo_thick[2];          // x distance from my edge particle to the far end of the halo on that side (+inf: wall)
     int mass_differs;              // upload: some particle's mass is not the first particle's (cleared by the upload)
     // statistics, one atomic per warp spread over kStatBins addresses (a single address would serialise
     // two million atomics per launch and cost more than a millisecond at 64 Mi particles)
@@ -1301,6 +1302,12 @@ __device__ __forceinline__ void slab_unpack_body(const SlabArgs &A, int what, co
                 if (bad) raise(ctl, E_UNSORTED, own0);
             }
         }
+        // how far the halo reaches from my edge particle: a smoothing length anywhere in the run whose support is
+        // wider than this could interact across the halo unseen (checked with the all-reduced h maximum)
+        __syncthreads();
+        if (threadIdx.x == 0 && cnt > 0 && A.na > 0)
+            ctl->halo_thick[A.side < 0 ? 0 : 1] = A.side < 0 ? (A.x[A.pad] - A.x[A.pad - cnt])
+                                                              : (A.x[A.pad + A.na + cnt - 1] - A.x[A.pad + A.na - 1]);
     }
     if (what == MSG_ITERATE && s_changed) {
         // queue those tiles for the next sweep, exactly like a changed particle of my own would
@@ -1328,7 +1335,10 @@ __global__ void __launch_bounds__(1024) k_slab_unpack2(SlabArgs A, int what, con
     slab_unpack_body(A, what, buf);
 }
 
-__global__ void k_slab_flags(Ctl *ctl, int hl, int hr) { ctl->halo_left = hl; ctl->halo_right = hr; }
+__global__ void k_slab_flags(Ctl *ctl, int hl, int hr) {
+    ctl->halo_left = hl; ctl->halo_right = hr;
+    ctl->halo_thick[0] = INFINITY; ctl->halo_thick[1] = INFINITY;
+}
 
 // ------------------------------------------------------------------------------------
 // Conservation diagnostics over the alive particles (the checks the reference's author wished for,

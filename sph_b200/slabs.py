@@ -98,9 +98,9 @@ class SlabRank(Simulation):
         self._check(getattr(self.L, "sphb_slab_" + name)(self.h, *args))
 
     def poll(self):
-        flags = (C.c_int * 3)()
+        flags = (C.c_int * 4)()
         self._check(self.L.sphb_slab_poll(self.h, flags))
-        return [flags[0], flags[1], flags[2]]
+        return [flags[0], flags[1], flags[2], flags[3]]
 
 
 def _fields_by_index(ranks):
@@ -169,8 +169,8 @@ class DistTransport:
         import torch
         import torch.distributed as dist
         self.r, self.dist = rank_obj, dist
-        self.flag = torch.zeros(3, dtype=torch.int32, device=rank_obj.device)
-        self.host_flag = torch.zeros(3, dtype=torch.int32).pin_memory()
+        self.flag = torch.zeros(4, dtype=torch.int32, device=rank_obj.device)
+        self.host_flag = torch.zeros(4, dtype=torch.int32).pin_memory()
 
     def exchange(self, what):
         r = self.r
@@ -256,8 +256,8 @@ class SlabSimulation:
         return self.fixed_rounds + 1
 
     def _flags(self):
-        """MAX over all ranks of (device error, order broken, halo changed): the step's host sync."""
-        fl = [0, 0, 0]
+        """MAX over all ranks of (device error, order broken, halo changed, largest h): the step's host sync."""
+        fl = [0, 0, 0, 0]
         for r in self.ranks:
             f = r.poll()
             fl = [max(a, b) for a, b in zip(fl, f)]
@@ -268,7 +268,7 @@ class SlabSimulation:
         for _ in range(nsteps):
             self._all("step_begin")
             rounds = self._attempt()
-            (err, unsorted, changed), mine = self._flags()
+            (err, unsorted, changed, hbits), mine = self._flags()
             for _repair in range(2):
                 if not unsorted:
                     break
@@ -277,7 +277,7 @@ class SlabSimulation:
                 # (nothing of the previous state has been overwritten)
                 self._all("resort")
                 rounds = self._attempt()
-                (err, unsorted, changed), mine = self._flags()
+                (err, unsorted, changed, hbits), mine = self._flags()
             if unsorted:
                 raise SphbError(11, "x-order still broken after the sort")
             while changed and not err:
@@ -286,11 +286,13 @@ class SlabSimulation:
                 self._all("refine")
                 self._exchange(MSG_ITERATE)
                 rounds += 1
-                (err, unsorted, changed), mine = self._flags()
+                (err, unsorted, changed, hbits), mine = self._flags()
             if err:
                 for r in self.ranks:
                     r.call("raise")          # raises SphbError with the device's message on the rank that has it
                 raise SphbError(err, "a neighbouring slab reported device error %d" % err)
+            for r in self.ranks:     # the widest kernel support anywhere in the run must fit inside every halo
+                r._check(r.L.sphb_slab_check_halo(r.h, hbits))
             self.rounds_last = rounds
             self._all("step_end")
 

@@ -63,10 +63,10 @@ def _routing_worker(rank, world, port, q):
             ok &= bool((recv[RIGHT] == 10.0 * (rank + 1) - 1).all())
         else:
             ok &= bool((recv[RIGHT] == 0).all())
-        flag = torch.zeros(3, dtype=torch.int32)
-        # one rank saw a change, another an error code: everybody learns both
-        ok &= agree_max(dist, flag, [13 if rank == 0 else 0, 0, 1 if rank == world - 1 else 0]) == [13, 0, 1]
-        ok &= agree_max(dist, flag, [0, 0, 0]) == [0, 0, 0]
+        flag = torch.zeros(4, dtype=torch.int32)
+        # one rank saw a change, another an error code, each its own h maximum: everybody learns the maxima
+        ok &= agree_max(dist, flag, [13 if rank == 0 else 0, 0, 1 if rank == world - 1 else 0, 100 + rank]) == [13, 0, 1, 99 + world]
+        ok &= agree_max(dist, flag, [0, 0, 0, 0]) == [0, 0, 0, 0]
         q.put((rank, ok))
     finally:
         dist.destroy_process_group()
