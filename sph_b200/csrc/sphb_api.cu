@@ -438,10 +438,14 @@ SweepArgs step_sweep_args(sphb_handle *H) {
     return A;
 }
 
-int step_force_first(sphb_handle *H) {
+int launch_step_first(sphb_handle *H) {   // the first force sweep of a step, on H->stream, tiles per H->part
     SweepArgs A = step_sweep_args(H);
-    if (H->opt.order == SPHB_ORDER_JACOBI) TRY(launch_first_sel<SEL_ALIVE>(H, A));
-    else TRY(launch_first_sel<SEL_INDEX>(H, A));
+    if (H->opt.order == SPHB_ORDER_JACOBI) return launch_first_sel<SEL_ALIVE>(H, A);
+    return launch_first_sel<SEL_INDEX>(H, A);
+}
+
+int step_force_first(sphb_handle *H) {
+    TRY(launch_step_first(H));
     phase_end(H, 4);
     return SPHB_OK;
 }
@@ -681,23 +685,37 @@ int on_comm_stream(sphb_handle *H, F fn) {
 // force kernels; only the tiles that can see a pad ("edge": K + one tile of particles at each end)
 // wait for them.
 int native_attempt(sphb_handle *H, int *rounds) {
+    // Two streams.  The communication stream does the BASE exchange, the density of the edge tiles, the RECORDS
+    // exchange and the first sweep of the edge tiles; the main stream does the interior tiles.  Each side waits
+    // for the other exactly where a tile reads its neighbour tile's results.
     CK(cudaEventRecord(H->ev_kick, H->stream));
     CK(cudaStreamWaitEvent(H->comm_stream, H->ev_kick, 0));
-    TRY(on_comm_stream(H, [&] { return native_exchange(H, MSG_BASE); }));
-    CK(cudaEventRecord(H->ev_base, H->comm_stream));
+    TRY(on_comm_stream(H, [&]() -> int {
+        TRY(native_exchange(H, MSG_BASE));
+        H->part = 2;
+        const int rc = launch_density(H, 1, 0, 1, H->Pn);          // edge tiles, halo in place
+        H->part = 0;
+        return rc;
+    }));
+    CK(cudaEventRecord(H->ev_edge, H->comm_stream));               // edge density done
     H->part = 1; TRY(launch_density(H, 1, 0, 1, H->Pn));            // interior tiles
-    CK(cudaStreamWaitEvent(H->stream, H->ev_base, 0));
-    H->part = 2; TRY(launch_density(H, 1, 0, 1, H->Pn));            // edge tiles, halo in place
     H->part = 0;
+    CK(cudaEventRecord(H->ev_base, H->stream));                     // interior density done
+    TRY(on_comm_stream(H, [&]() -> int {
+        TRY(native_exchange(H, MSG_RECORDS));
+        CK(cudaStreamWaitEvent(H->comm_stream, H->ev_base, 0));     // edge tiles read interior records next to them
+        H->part = 2;
+        const int rc = launch_step_first(H);
+        H->part = 0;
+        return rc;
+    }));
+    CK(cudaEventRecord(H->ev_rec, H->comm_stream));                 // edge first sweep done
+    CK(cudaStreamWaitEvent(H->stream, H->ev_edge, 0));              // interior tiles read edge records next to them
     phase_end(H, 3);
-    CK(cudaEventRecord(H->ev_edge, H->stream));
-    CK(cudaStreamWaitEvent(H->comm_stream, H->ev_edge, 0));
-    TRY(on_comm_stream(H, [&] { return native_exchange(H, MSG_RECORDS); }));
-    CK(cudaEventRecord(H->ev_rec, H->comm_stream));
-    H->part = 1; TRY(step_force_first(H));
-    CK(cudaStreamWaitEvent(H->stream, H->ev_rec, 0));
-    H->part = 2; TRY(step_force_first(H));
+    H->part = 1; TRY(launch_step_first(H));
     H->part = 0;
+    CK(cudaStreamWaitEvent(H->stream, H->ev_rec, 0));
+    phase_end(H, 4);
     TRY(step_refine(H));
     for (int r = 0; r < H->fixed_rounds; r++) {
         TRY(native_exchange(H, MSG_ITERATE));
