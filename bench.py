@@ -45,6 +45,11 @@ WORKLOADS = {
     "colliding_streams_isothermal_fixedh_n1m": (1024 * 1024, 0, False),       # configs[1]
     "colliding_streams_adiabatic_varh_n256m": (256 * 1024 * 1024, 1, True),   # configs[4]
     "colliding_streams_adiabatic_varh_n1m": (1024 * 1024, 1, True),
+    # generic particle counts: the lattice positions are not exactly equidistant in floating point, so every
+    # particle of the undisturbed streams feels a rounding-level kick and the ordered sweep has work everywhere
+    "colliding_streams_adiabatic_varh_n64000000": (64_000_000, 1, True),
+    "colliding_streams_adiabatic_varh_n16000000": (16_000_000, 1, True),
+    "colliding_streams_isothermal_fixedh_n1000000": (1_000_000, 0, False),
 }
 DEFAULT_WORKLOAD = "colliding_streams_adiabatic_varh_n64m"
 
@@ -211,7 +216,9 @@ def run_ours(args, name, n, pc, varh):
     cfg = Config(n_part=n, mass=kw["mass"], pressure_calc=pc, t_i=kw["t_i"])
     from sph_b200.slabs import make_simulation   # 1 rank: a plain Simulation; >1: this rank's x-slab
     sim = make_simulation(cfg, variable_h=varh, fixed_h=kw["constant_h"], device=local, rank=rank, world=world,
-                          halo_count=args.halo, native=not args.torch_exchange, sweep_rel_tol=args.sweep_tol)
+                          halo_count=args.halo, native=not args.torch_exchange, sweep_rel_tol=args.sweep_tol,
+                          sweep_mode=args.sweep_mode, sweep_group=args.sweep_group, sweep_segment=args.sweep_segment,
+                          sweep_burn_in=args.sweep_burn_in)
     if world > 1:
         stream = sim.stream                      # handle, halo messages and NCCL calls share it
     else:
@@ -373,6 +380,9 @@ def run_ours(args, name, n, pc, varh):
                                  "reference (index-ordered in-place sweep, converged to %.1e relative)" % args.sweep_tol), "sweeps_per_step": sweeps_mean,
                        "parallelism": ("x-slabs x%d, %d-particle halos over ncclSend/ncclRecv, %d ITERATE exchanges in the last step"
                                        % (world, args.halo, rounds_last)) if world > 1 else "single GPU",
+                       "sweep": {"serial_steps": c2.sweep_steps, "group": c2.sweep_group, "segment": c2.sweep_segment,
+                                 "burn_in": c2.sweep_burn_in, "flagged": c2.sweep_flagged, "verify_fail": c2.sweep_verify_fail,
+                                 "refine_tiles": c2.refine_tiles, "refine_tile_evals": c2.refine_tile_evals},
                        "l2": "state arrays (%.1f GB) larger than L2, no flush needed" % (n * 8 * 20 / 1e9)},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
     print(json.dumps(line), flush=True)
@@ -390,6 +400,10 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sweep-tol", type=float, default=0.0,
                     help="0 (default): the ordered sweep is iterated to its bitwise fixed point; > 0: relative tolerance")
+    ap.add_argument("--sweep-mode", type=int, default=0, help="ordered sweep: 0 auto, 1 work lists, 2 serial sweep")
+    ap.add_argument("--sweep-group", type=int, default=0)
+    ap.add_argument("--sweep-segment", type=int, default=0)
+    ap.add_argument("--sweep-burn-in", type=int, default=0)
     ap.add_argument("--torch-exchange", action="store_true",
                     help="x-slab runs: drive the halo exchange from Python (torch.distributed) instead of inside libsphb")
     ap.add_argument("--halo", type=int, default=256, help="particles exchanged per slab edge (x-slab runs)")

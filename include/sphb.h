@@ -65,8 +65,18 @@ typedef struct sphb_options {
                              reference's sequential result exactly; > 0 stops once no kicked v, u moves by more than this
                              relative amount (v against max(|v|, c_s)): bounded deviation, far fewer sweeps when every
                              particle's kick is non-zero */
-    int reserved[6];
+    int sweep_mode;      /* SPHB_ORDER_REFERENCE: how the ordered sweep is computed.  Every choice gives the same bits (the
+                            reference's sequential result); they differ in cost only.  SPHB_SWEEP_AUTO (default) picks per
+                            step; SPHB_SWEEP_WORKLIST: first guess for all particles, then fixed-point refinement of the
+                            tiles in reach of a changed particle (cheap while almost no kick is non-zero);
+                            SPHB_SWEEP_SERIAL: one pass in which groups of lanes walk segments of the x-sorted array
+                            left to right (cost independent of the state) */
+    int sweep_group;     /* serial sweep: lanes per group, 8 or 16 (slots a particle looks back / ahead = lanes - 1); 0 = auto */
+    int sweep_segment;   /* serial sweep: particles per segment; 0 = auto */
+    int sweep_burn_in;   /* serial sweep: particles a segment starts early; 0 = auto (grows when its check fails) */
+    int reserved[2];
 } sphb_options;
+enum { SPHB_SWEEP_AUTO = 0, SPHB_SWEEP_WORKLIST = 1, SPHB_SWEEP_SERIAL = 2 };
 
 typedef struct sphb_counters {
     int n_alive;
@@ -86,6 +96,10 @@ typedef struct sphb_counters {
                                    the final one where the last Newton step was below 1e-12 and the sums were reused) */
     int refine_tiles;           /* most recent step: tiles the ordered-sweep refinement took from its work lists */
     int refine_tile_evals;      /* ... and how often it evaluated them, in-tile iterations included */
+    long long sweep_steps;      /* steps whose ordered sweep was done by the serial-sweep kernel */
+    int sweep_group, sweep_segment, sweep_burn_in;   /* its geometry in the most recent step (0: that step used work lists) */
+    int sweep_flagged;          /* most recent step: particles it handed to the work-list refinement */
+    int sweep_verify_fail;      /* most recent step: burn-in values that differed from the left segment's final ones */
 } sphb_counters;
 
 /* status codes */

@@ -13,6 +13,7 @@ _ROOT = os.path.dirname(_HERE)
 
 ISOTHERMAL, ADIABATIC = 0, 1
 ORDER_REFERENCE, ORDER_JACOBI = 0, 1
+SWEEP_AUTO, SWEEP_WORKLIST, SWEEP_SERIAL = 0, 1, 2
 PHASES = ("kick_drift", "sort", "ghosts", "density", "force_first", "force_refine")
 FIELDS = ("mass", "pos", "vel", "acc", "h", "du_dt", "u", "density", "pressure")
 
@@ -36,7 +37,8 @@ class SphbOptions(C.Structure):
     _fields_ = [("variable_h", C.c_int), ("fixed_h", C.c_double), ("order", C.c_int),
                 ("max_sweeps", C.c_int), ("device", C.c_int), ("pad_capacity", C.c_int),
                 ("capacity", C.c_int), ("sort_every_step", C.c_int), ("sweep_rel_tol", C.c_double),
-                ("reserved", C.c_int * 6)]
+                ("sweep_mode", C.c_int), ("sweep_group", C.c_int), ("sweep_segment", C.c_int),
+                ("sweep_burn_in", C.c_int), ("reserved", C.c_int * 2)]
 
 
 class SphbCounters(C.Structure):
@@ -45,7 +47,9 @@ class SphbCounters(C.Structure):
                 ("fallbacks", C.c_longlong), ("newton_hist", C.c_longlong * 12),
                 ("nbr_min", C.c_int), ("nbr_max", C.c_int), ("nbr_mean", C.c_double),
                 ("h_max", C.c_double), ("launches", C.c_longlong), ("force_pairs_mean", C.c_double),
-                ("density_scans_mean", C.c_double), ("refine_tiles", C.c_int), ("refine_tile_evals", C.c_int)]
+                ("density_scans_mean", C.c_double), ("refine_tiles", C.c_int), ("refine_tile_evals", C.c_int),
+                ("sweep_steps", C.c_longlong), ("sweep_group", C.c_int), ("sweep_segment", C.c_int),
+                ("sweep_burn_in", C.c_int), ("sweep_flagged", C.c_int), ("sweep_verify_fail", C.c_int)]
 
 
 assert C.sizeof(SphbConfig) == 64
@@ -87,6 +91,12 @@ class Counters:
     density_scans_mean: float = 0.0
     refine_tiles: int = 0
     refine_tile_evals: int = 0
+    sweep_steps: int = 0
+    sweep_group: int = 0
+    sweep_segment: int = 0
+    sweep_burn_in: int = 0
+    sweep_flagged: int = 0
+    sweep_verify_fail: int = 0
 
 
 class SphbError(RuntimeError):
@@ -192,7 +202,7 @@ class Simulation:
 
     def __init__(self, config: Config, variable_h=True, fixed_h=0.2, order=ORDER_REFERENCE,
                  max_sweeps=64, device=-1, pad_capacity=4096, capacity=0, sort_every_step=False,
-                 sweep_rel_tol=0.0):
+                 sweep_rel_tol=0.0, sweep_mode=SWEEP_AUTO, sweep_group=0, sweep_segment=0, sweep_burn_in=0):
         self.L = load_library()
         self.config = config
         opt = SphbOptions()
@@ -206,6 +216,8 @@ class Simulation:
         opt.capacity = capacity
         opt.sort_every_step = int(sort_every_step)
         opt.sweep_rel_tol = float(sweep_rel_tol)
+        opt.sweep_mode, opt.sweep_group = int(sweep_mode), int(sweep_group)
+        opt.sweep_segment, opt.sweep_burn_in = int(sweep_segment), int(sweep_burn_in)
         self.h = C.c_void_p()
         cfg = config.to_c()
         rc = self.L.sphb_create(C.byref(cfg), C.byref(opt), C.byref(self.h))
@@ -301,7 +313,9 @@ class Simulation:
         self._check(self.L.sphb_get_counters(self.h, C.byref(c)))
         return Counters(c.n_alive, c.n_ghost, c.steps, c.sweeps_total, c.sweeps_last, c.sorts,
                         c.fallbacks, list(c.newton_hist), c.nbr_min, c.nbr_max, c.nbr_mean, c.h_max,
-                        c.launches, c.force_pairs_mean, c.density_scans_mean, c.refine_tiles, c.refine_tile_evals)
+                        c.launches, c.force_pairs_mean, c.density_scans_mean, c.refine_tiles, c.refine_tile_evals,
+                        c.sweep_steps, c.sweep_group, c.sweep_segment, c.sweep_burn_in, c.sweep_flagged,
+                        c.sweep_verify_fail)
 
     def diagnostics(self):
         """{mass, momentum, kinetic, thermal} totals over the alive particles (sphb_diagnostics)."""

@@ -41,6 +41,16 @@ struct sphb_handle {
         *perm = nullptr, *iota = nullptr, *wl0 = nullptr, *wl1 = nullptr, *wl2 = nullptr;
     int refine_peak = 0;      // largest refinement work list of the previous step
     Rec2 *rec = nullptr;      // force-pass records written by the density pass
+    // serial sweep (k_force_sweep): per-tile h maximum of the density pass, burn-in results kept for the check
+    unsigned *thm = nullptr;
+    double *scr = nullptr;
+    size_t scr_cap = 0;       // doubles
+    bool sweep_on = true;     // strategy of the next step in auto mode: serial sweep (true) or work lists (false)
+    bool sweep_used = false;  // ... and what the step in flight uses
+    int sw_G = 8, sw_L = 0, sw_B = 0, sw_nseg = 0;
+    int sweep_blocks[2] = {0, 0};   // resident CTAs per SM of the G = 8 / G = 16 kernels (0 = not asked yet)
+    long long sweep_steps = 0;
+    int sweep_flagged_last = 0, sweep_verify_fail_last = 0, sweep_burn_in_last = 0;
     double *gsum = nullptr;   // own-h gradient sums written by the density pass
     // ghost staging (2*pad each)
     double *gx = nullptr, *gv = nullptr, *gu = nullptr, *ga = nullptr, *gdu = nullptr, *gh = nullptr,
@@ -267,6 +277,7 @@ int launch_density(sphb_handle *H, int root_alive, int root_ghosts, int check_ol
     A.cnt = H->cnt; A.ctl = H->d_ctl; A.pad = H->pad; A.na = H->na;
     A.limit = H->cfg.limit; A.hfac = H->cfg.h_factor; A.m0 = H->m0;
     A.root_ghosts = root_ghosts; A.root_alive = root_alive; A.check_old = check_old;
+    A.thm = H->thm;
     const int ntot = nblk(H->na + 2 * H->pad, kTile);
     // tile ranges [begin, end) to launch: everything, or (x-slab overlap) the interior / the two edges;
     // edge = every tile that can see a pad: the pads themselves plus K + one tile of own particles
@@ -354,6 +365,84 @@ int launch_refine(sphb_handle *H, SweepArgs A) {
     return SPHB_OK;
 }
 
+SweepArgs step_sweep_args(sphb_handle *H);
+
+template <int G>
+int sweep_occupancy(sphb_handle *H, bool adia, int *blocks) {
+    const size_t smem = (size_t)(kSweepThreads / G) * sizeof(SweepGrp<G>);
+    const void *fn = adia ? (const void *)k_force_sweep<true, G> : (const void *)k_force_sweep<false, G>;
+    CK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks, fn, kSweepThreads, smem));
+    if (*blocks < 1) { H->err = "serial sweep kernel cannot be made resident"; return SPHB_ERR_CUDA; }
+    return SPHB_OK;
+}
+
+// Does the step in flight use the serial sweep, and with what geometry?  Group width G: 8 lanes look 7 slots
+// back and ahead (variable h keeps ~5 neighbours per side), 16 lanes 15 (fixed h of 5 spacings: 12 per side).
+// Burn-in B: the left boundary's influence falls by an order of magnitude per neighbour hop, 16 decades need
+// about 16 hops of up to (neighbours per side) slots.  Segment length L: long enough to make the burn-in cheap,
+// short enough to give every resident group a segment, and a whole number of waves.
+int sweep_plan(sphb_handle *H) {
+    H->sweep_used = false;
+    if (H->opt.order != SPHB_ORDER_REFERENCE || !H->uniform_mass || H->opt.sweep_mode == SPHB_SWEEP_WORKLIST) return SPHB_OK;
+    if (H->slab) return SPHB_OK;
+    if (H->opt.sweep_mode == SPHB_SWEEP_AUTO && !H->sweep_on) return SPHB_OK;
+    if (H->na < 2) return SPHB_OK;
+    const bool adia = H->cfg.pressure_calc == SPHB_ADIABATIC;
+    const int G = H->opt.sweep_group == 16 ? 16 : (H->opt.sweep_group == 8 ? 8 : (H->opt.variable_h ? 8 : 16));
+    int &blocks = H->sweep_blocks[G == 16 ? 1 : 0];
+    if (!blocks) { if (G == 8) TRY(sweep_occupancy<8>(H, adia, &blocks)); else TRY(sweep_occupancy<16>(H, adia, &blocks)); }
+    int B = H->opt.sweep_burn_in > 0 ? H->opt.sweep_burn_in : (H->sweep_burn_in_last ? H->sweep_burn_in_last : (G == 8 ? 64 : 192));
+    B = std::max(G, (B + G - 1) / G * G);
+    int L = H->opt.sweep_segment;
+    if (L <= 0) {
+        const long long resident = (long long)H->num_sms * blocks * (kSweepThreads / G);
+        const long long lmax = 2048;
+        const long long waves = std::max(1ll, (H->na + resident * lmax - 1) / (resident * lmax));
+        L = (int)((H->na + resident * waves - 1) / (resident * waves));
+        L = std::max(L, 4 * B);                          // burn-in at most a quarter of the work
+    }
+    L = std::max(B, (L + G - 1) / G * G);
+    H->sw_G = G; H->sw_L = L; H->sw_B = B; H->sw_nseg = nblk(H->na, L);
+    if ((size_t)H->sw_nseg * 2 * (G - 1) > H->scr_cap) return SPHB_OK;   // cannot happen with the sizes of sphb_create
+    H->sweep_used = true;
+    return SPHB_OK;
+}
+
+int launch_sweep(sphb_handle *H) {
+    SerialArgs K;
+    K.S = step_sweep_args(H);
+    K.thm = H->thm; K.nthm = nblk(H->na + 2 * H->pad, kTile);
+    K.scr = H->scr; K.L = H->sw_L; K.B = H->sw_B; K.nseg = H->sw_nseg;
+    const bool adia = H->cfg.pressure_calc == SPHB_ADIABATIC;
+    if (H->sw_G == 8) {
+        const int gpb = kSweepThreads / 8;
+        const size_t smem = (size_t)gpb * sizeof(SweepGrp<8>);
+        if (adia) k_force_sweep<true, 8><<<nblk(K.nseg, gpb), kSweepThreads, smem, H->stream>>>(K);
+        else k_force_sweep<false, 8><<<nblk(K.nseg, gpb), kSweepThreads, smem, H->stream>>>(K);
+    } else {
+        const int gpb = kSweepThreads / 16;
+        const size_t smem = (size_t)gpb * sizeof(SweepGrp<16>);
+        if (adia) k_force_sweep<true, 16><<<nblk(K.nseg, gpb), kSweepThreads, smem, H->stream>>>(K);
+        else k_force_sweep<false, 16><<<nblk(K.nseg, gpb), kSweepThreads, smem, H->stream>>>(K);
+    }
+    H->launches++;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
+int launch_sweep_verify(sphb_handle *H) {
+    if (H->sw_nseg < 2) return SPHB_OK;
+    SerialArgs K;
+    K.S = step_sweep_args(H);
+    K.thm = H->thm; K.nthm = 0; K.scr = H->scr; K.L = H->sw_L; K.B = H->sw_B; K.nseg = H->sw_nseg;
+    const int R = H->sw_G - 1;
+    k_sweep_verify<<<nblk((H->sw_nseg - 1) * R, 256), 256, 0, H->stream>>>(K, R);
+    H->launches++;
+    CK(cudaGetLastError());
+    return SPHB_OK;
+}
+
 SweepArgs sweep_args(sphb_handle *H) {
     SweepArgs A;
     A.F.x = H->x; A.F.idx = H->idx; A.F.m = H->m;
@@ -375,6 +464,7 @@ SweepArgs sweep_args(sphb_handle *H) {
 // after the drift run again; nothing of the previous state has been overwritten by then.
 int step_begin(sphb_handle *H) {   // kick-drift + order flag, wall ghosts
     H->resorts_this_step = 0;
+    H->sweep_used = false;
     if (H->epoch > 0x7fff0000 - 4 * H->opt.max_sweeps) {   // stamp wrap-around
         CK(cudaMemsetAsync(H->dirty, 0, sizeof(int) * (size_t)nblk(H->cap_alive, kTile), H->stream));
         H->epoch = 8;
@@ -445,13 +535,16 @@ int launch_step_first(sphb_handle *H) {   // the first force sweep of a step, on
 }
 
 int step_force_first(sphb_handle *H) {
-    TRY(launch_step_first(H));
+    TRY(sweep_plan(H));
+    if (H->sweep_used) TRY(launch_sweep(H));           // the ordered sweep in one pass
+    else TRY(launch_step_first(H));                    // first guess for everybody, work lists for the refinement
     phase_end(H, 4);
     return SPHB_OK;
 }
 
-int step_refine(sphb_handle *H) {   // runs until this handle's work list is empty
+int step_refine(sphb_handle *H, bool after_sweep = true) {   // runs until this handle's work list is empty
     if (H->opt.order == SPHB_ORDER_JACOBI) return SPHB_OK;
+    if (H->sweep_used && after_sweep) TRY(launch_sweep_verify(H));
     SweepArgs A = step_sweep_args(H);
     A.F.vA = H->vn; A.F.uA = H->un;   // lower-index neighbours are seen fully kicked
     TRY(launch_refine(H, A));
@@ -493,6 +586,25 @@ int step_finish(sphb_handle *H) {
     const int used = (H->opt.order == SPHB_ORDER_JACOBI) ? 1 : H->h_ctl->sweeps_used;
     H->sweeps_last = used;
     H->sweeps_total += used;
+    // Strategy of the next step (auto mode).  The serial sweep costs the same whatever the state; the work lists cost
+    // next to nothing while almost no particle feels a non-zero kick (the undisturbed lattice with dyadic
+    // positions) and many times a sweep once every particle does.
+    if (H->opt.order == SPHB_ORDER_REFERENCE) {
+        const int ntiles = nblk(H->na, kTile);
+        if (H->sweep_used) {
+            H->sweep_steps++;
+            H->sweep_flagged_last = H->h_ctl->sweep_flagged;
+            H->sweep_verify_fail_last = H->h_ctl->sweep_verify_fail;
+            H->sweep_burn_in_last = H->sw_B;
+            // a burn-in that failed its check somewhere was too short for this state: lengthen it
+            if (H->h_ctl->sweep_verify_fail > 0 && H->opt.sweep_burn_in <= 0)
+                H->sweep_burn_in_last = std::min(2 * H->sw_B, 512);
+            // every chunk with a non-zero kick would have put at least one tile on a work list
+            if (H->h_ctl->sweep_moved_chunks < ntiles / 16) H->sweep_on = false;
+        } else if (H->h_ctl->tiles_swept > ntiles / 8 + 16) {
+            H->sweep_on = true;
+        }
+    }
     H->cfg.n_ghost = wall_ghosts(H);
     H->cfg.n_part = H->na + H->cfg.n_ghost;
     phase_collect(H);
@@ -783,7 +895,11 @@ int sphb_create(const sphb_config *cfg, const sphb_options *opt_in, sphb_handle 
     sphb_options opt;
     if (opt_in) opt = *opt_in; else sphb_default_options(&opt);
     if (cfg->n_part < 1 || cfg->n_ghost < 0 || cfg->n_ghost > cfg->n_part) { H->err = "bad n_part / n_ghost"; return SPHB_ERR_INVALID; }
-    if (opt.pad_capacity < 1 || opt.max_sweeps < 1 || !(opt.sweep_rel_tol >= 0.0)) { H->err = "bad options"; return SPHB_ERR_INVALID; }
+    if (opt.pad_capacity < 1 || opt.max_sweeps < 1 || !(opt.sweep_rel_tol >= 0.0) || opt.sweep_mode < 0 || opt.sweep_mode > 2 ||
+        (opt.sweep_group != 0 && opt.sweep_group != 8 && opt.sweep_group != 16) || opt.sweep_segment < 0 || opt.sweep_burn_in < 0) {
+        H->err = "bad options";
+        return SPHB_ERR_INVALID;
+    }
     if (cfg->pressure_calc != SPHB_ISOTHERMAL && cfg->pressure_calc != SPHB_ADIABATIC) {
         H->err = "Unknown pressure calculation mode!";   // calculators.cpp:80-82
         return SPHB_ERR_INVALID;
@@ -834,6 +950,9 @@ int sphb_create(const sphb_config *cfg, const sphb_options *opt_in, sphb_handle 
     rc |= dalloc(H, &H->wl0, (size_t)nblk(H->cap_alive, kTile) + 1); rc |= dalloc(H, &H->wl1, (size_t)nblk(H->cap_alive, kTile) + 1);
     rc |= dalloc(H, &H->wl2, (size_t)nblk(H->cap_alive, kTile) + 1);
     rc |= dalloc(H, &H->rec, T); rc |= dalloc(H, &H->gsum, T);
+    rc |= dalloc(H, &H->thm, (size_t)nblk(H->total, kTile) + 2);
+    H->scr_cap = ((size_t)H->cap_alive / 8 + 2) * 2 * 15;     // segments are never shorter than 8 particles
+    rc |= dalloc(H, &H->scr, H->scr_cap);
     if (rc) return fail(SPHB_ERR_CUDA);
     CKC(cudaMallocHost((void **)&H->h_ctl, sizeof(Ctl)));
     memset(H->h_ctl, 0, sizeof(Ctl));
@@ -857,7 +976,7 @@ void sphb_destroy(sphb_handle *H) {
                     H->hn, H->rhon, H->omn, H->oms, H->Pn, H->tmp, H->gx, H->gv, H->gu, H->ga, H->gdu, H->gh,
                     H->grho, H->gP, H->gm, H->idx, H->idx_alt, H->slot_id, H->cnt, H->dirty, H->cand, H->gorder,
                     H->perm, H->iota, H->gkey, H->d_ctl, H->cub_tmp, H->d_aos, H->d_newton, H->d_nbr,
-                    H->wl0, H->wl1, H->wl2, H->rec, H->gsum};
+                    H->wl0, H->wl1, H->wl2, H->rec, H->gsum, H->thm, H->scr};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (H->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(H->comm);
     for (int w = 0; w < 3; w++) for (int k = 0; k < 2; k++) { if (H->msg_send[w][k]) cudaFree(H->msg_send[w][k]); if (H->msg_recv[w][k]) cudaFree(H->msg_recv[w][k]); }
@@ -1379,6 +1498,12 @@ int sphb_get_counters(sphb_handle *H, sphb_counters *out) {
     out->density_scans_mean = (H->na + out->n_ghost) ? (double)scans / (H->na + H->h_ctl->GL + H->h_ctl->GR) : 0.0;
     out->refine_tiles = H->h_ctl->tiles_swept;
     out->refine_tile_evals = H->h_ctl->tile_evals;
+    out->sweep_steps = H->sweep_steps;
+    out->sweep_group = H->sweep_used ? H->sw_G : 0;
+    out->sweep_segment = H->sweep_used ? H->sw_L : 0;
+    out->sweep_burn_in = H->sweep_used ? H->sw_B : 0;
+    out->sweep_flagged = H->sweep_used ? H->h_ctl->sweep_flagged : 0;
+    out->sweep_verify_fail = H->sweep_used ? H->h_ctl->sweep_verify_fail : 0;
     if (H->have_counts) {
         const int n = H->na;
         std::vector<int> nw((size_t)n + 2 * H->pad), nb((size_t)n + 2 * H->pad);
@@ -1426,7 +1551,8 @@ int sphb_get_phase_times(sphb_handle *H, double *ms, long long *launches, int re
 // work arrays k_density writes besides its outputs (omega of the new and of the old
 // state, packed iteration / neighbour counts) plus the control block live in ONE
 // file-scope device array of fixed size, which every GPU that loads libsphb.so keeps
-// until the process exits (20 MiB + 256 B).
+// until the process exits (20 MiB for the work arrays plus the control block rounded up to 256 B,
+// about 1.5 KiB today; the size follows sizeof(Ctl), see kStaticCtlBytes).
 //
 // Rules that follow from the shared array:
 //   * n is limited to SPHB_STATIC_MAX_PARTICLES; larger calls are refused, nothing runs.
@@ -1440,7 +1566,10 @@ int sphb_get_phase_times(sphb_handle *H, double *ms, long long *launches, int re
 //     starting any stream capture.
 // No cudaMalloc / cudaFree / allocating library routine is called on this path.
 namespace {
-constexpr size_t kStaticCtlBytes = 256;
+// the control block's share of the array follows the struct (it holds the 64-bin statistics): the work
+// arrays start at the next 256-byte boundary, so nothing the kernel writes into Ctl can reach them
+constexpr size_t kStaticCtlBytes = (sizeof(Ctl) + 255) & ~(size_t)255;
+static_assert(sizeof(Ctl) <= kStaticCtlBytes && kStaticCtlBytes % 256 == 0, "control block must fit its region");
 constexpr size_t kStaticBytes = kStaticCtlBytes + (size_t)SPHB_STATIC_MAX_PARTICLES * (8 + 8 + 4);
 // In host code this name is only a stand-in for the symbol: it is NOT a device address.
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
@@ -1484,6 +1613,7 @@ int sphb_density_static(const double *d_x, const double *d_h, const double *d_rh
     A.cnt = cnt; A.ctl = ctl; A.pad = 0; A.na = n;
     A.limit = limit; A.hfac = h_factor; A.m0 = mass;
     A.root_ghosts = 0; A.root_alive = 1; A.check_old = 0;
+    A.thm = nullptr;
     const int grid = nblk(n, kTile);
     A.tile_base = 0;
     if (variable_h) k_density<true, true, false><<<grid, kTile, 0, st>>>(A);

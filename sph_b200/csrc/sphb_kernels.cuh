@@ -63,6 +63,10 @@ struct Ctl {
     int migrated;                  // particles that changed slab in the current attempt
     double halo_thick[2];          // x distance from my edge particle to the far end of the halo on that side (+inf: wall)
     int mass_differs;              // upload: some particle's mass is not the first particle's (cleared by the upload)
+    // serial sweep (k_force_sweep) of the current step
+    int sweep_flagged;             // tiles it handed to the work-list refinement (reach beyond its window, index inversions)
+    int sweep_verify_fail;         // segments whose burn-in did not reproduce the left segment's final values
+    int sweep_moved_chunks;        // chunks holding a particle whose second kick was not exactly zero
     // statistics, one atomic per warp spread over kStatBins addresses (a single address would serialise
     // two million atomics per launch and cost more than a millisecond at 64 Mi particles)
     unsigned long long force_pairs[kStatBins];   // (i,j) pairs evaluated by the first force sweep (self included)
@@ -244,6 +248,7 @@ struct DensityArgs {
     int root_alive;      // 0: omega-only pass (keeps h, rho; used by sphb_forces / sphb_omega)
     int check_old;       // 1: the old (h, rho) state is also seen by force sums (step path)
     int tile_base;       // the launch covers tiles tile_base + blockIdx.x (interior / edge launches of a slab)
+    unsigned *thm;       // per tile of kTile slots: largest h (old or new) in it as float bits rounded up; may be null
 };
 
 // Fused density + variable-h root-find + omega, one thread per
@@ -265,7 +270,10 @@ __global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs
     Ctl *ctl = A.ctl;
     const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
     const int t0 = (SLAB ? (int)blockIdx.x + A.tile_base : (int)blockIdx.x) * kTile;   // tiles of [0, pad + na + pad)
-    if (t0 >= hi || t0 + kTile <= lo) return;
+    if (t0 >= hi || t0 + kTile <= lo) {
+        if (A.thm && threadIdx.x == 0) A.thm[t0 / kTile] = 0u;
+        return;
+    }
     const int wbase = max(t0 - kDHalo, lo);
     const int wn = min(t0 + kTile + kDHalo, hi) - wbase;
     for (int k = threadIdx.x; k < wn; k += kTile) sx[k] = A.x[wbase + k];
@@ -445,6 +453,9 @@ __global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs
         const unsigned long long bits = (unsigned long long)__double_as_longlong((double)__uint_as_float(mx));
         // after the first CTAs the bound rarely grows: look before paying for an atomic on one hot address
         if (bits > *((volatile unsigned long long *)&ctl->hmax_bits)) atomicMax(&ctl->hmax_bits, bits);
+        // the serial sweep bounds its neighbour scan by the largest h of the tiles around a particle
+        // (a slab's halo slots are skipped above: their maximum arrives with the RECORDS message)
+        if (A.thm) { if (SLAB) atomicMax(A.thm + t0 / kTile, mx); else A.thm[t0 / kTile] = mx; }
     }
 }
 
@@ -506,9 +517,24 @@ struct Own {
 // + gradW(hbar) Pi_ij(c_ac)], accE gathers m_j v_ij gradW(hbar) [P_i/(rho_i^2 om_i) + Pi_ij(c_ec)/2],
 // both without the sign.  dir = +1 for a left neighbour (x_i - x_j = +ar), -1 for a right one.
 // Everything is written with hs = h_i + h_j = 2 hbar.
-template <bool ADIA, bool UM>
-__device__ __forceinline__ bool pair_terms(const Own<ADIA> &o, double ar, double dir, const Rec &rj, double vj,
-                                           double uj, double mj, double &accA, double &accE) {
+//
+// The pair is evaluated in two parts.  pair_geom: everything that depends on positions, smoothing
+// lengths, densities and omegas only (the reciprocal, both spline polynomials) — four numbers.
+// pair_apply: the part that needs the neighbour's velocity and energy, a dozen operations.  The
+// ordered sweep changes only (v_j, u_j) of a neighbour while it runs, so the serial sweep kernel
+// does the first part for all pairs of a chunk in parallel and only the second part along the
+// dependency chain.  Every force kernel goes through these two functions, in the same order of
+// accumulation (farthest neighbour first, per side), so a particle evaluated by any of them from
+// the same inputs gets the same bits.
+struct PairK {
+    double K2;     // mu_ij = K2 (v_i - v_j):  hbar r_ij / (r^2 + 0.01 hbar^2), signed
+    double irho;   // 1 / ((rho_i + rho_j) / 2)
+    double gb;     // |gradW(hbar)|
+    double G1;     // |gradW(h_j)| / (rho_j omega_j) (x (gamma - 1) when adiabatic): times u_j (adiabatic) it is the P_j term
+};
+
+template <bool ADIA>
+__device__ __forceinline__ bool pair_geom(const Own<ADIA> &o, double ar, double dir, const Rec &rj, PairK &k) {
     const double hs = o.h + rj.h;
     const double t1j = fma(2.5, rj.h, -ar), t1b = fma(1.25, hs, -ar);
     if (max(__double2hiint(t1j), __double2hiint(t1b)) < o.hi_eps) return false;   // beyond (or on the edge of) 2.5 h_j and 2.5 hbar
@@ -523,25 +549,30 @@ __device__ __forceinline__ bool pair_terms(const Own<ADIA> &o, double ar, double
     const double irs = t * D;
     const double ihs2 = ihs * ihs;
     // gradW(hbar) without its sign: -4 sigma / hbar^5 * poly = -128 sigma / hs^5 * poly
-    const double gb = dpoly_from(t1b, ar, hs, 0.75, 0.25, o.hi_eps) * ((32.0 * kGradC) * ((ihs2 * ihs2) * ihs));
-    const double PrRho_j = ADIA ? ((kGamma - 1) * uj) * rj.kap : rj.kap;
-    const double gj = dpoly_from(t1j, ar, rj.h, 1.5, 0.5, o.hi_eps) * (rj.c5 * PrRho_j);
+    k.gb = dpoly_from(t1b, ar, hs, 0.75, 0.25, o.hi_eps) * ((32.0 * kGradC) * ((ihs2 * ihs2) * ihs));
+    k.G1 = dpoly_from(t1j, ar, rj.h, 1.5, 0.5, o.hi_eps) * (rj.c5 * (ADIA ? (kGamma - 1) * rj.kap : rj.kap));
+    k.K2 = ((0.5 * hs) * (dir * ar)) * iD;
+    k.irho = 2.0 * irs;                   // 1 / ((rho_i + rho_j) / 2)
+    return true;
+}
+
+template <bool ADIA, bool UM>
+__device__ __forceinline__ void pair_apply(const Own<ADIA> &o, const PairK &k, double vj, double uj, double mj,
+                                           double &accA, double &accE) {
     const double v_ij = o.v - vj;
-    const double dot = v_ij * (dir * ar);
-    // artificial viscosity (calculators.cpp:148-172): alpha = 1, beta = 2, eta^2 = 0.01 hbar^2
+    const double mu = k.K2 * v_ij;        // same sign as v_ij . r_ij
+    // artificial viscosity (calculators.cpp:148-172): alpha = 1, beta = 2, eta^2 = 0.01 hbar^2; none for a receding pair
     double visc_ac = 0.0, visc_ec = 0.0;
-    if (!(dot > 0)) {
-        const double mu = ((0.5 * hs) * dot) * iD;
+    if (!(mu > 0)) {
         const double two_mu2 = 2.0 * (mu * mu);
-        const double irho = 2.0 * irs;               // 1 / ((rho_i + rho_j) / 2)
-        visc_ac = fma(-o.c_ac, mu, two_mu2) * irho;
-        visc_ec = fma(-o.c_ec, mu, two_mu2) * irho;
+        visc_ac = fma(-o.c_ac, mu, two_mu2) * k.irho;
+        visc_ec = fma(-o.c_ec, mu, two_mu2) * k.irho;
     }
-    const double ta = fma(gb, visc_ac, gj);
-    const double te = (v_ij * gb) * fma(0.5, visc_ec, o.PrRho);
+    const double gj = ADIA ? k.G1 * uj : k.G1;
+    const double ta = fma(k.gb, visc_ac, gj);
+    const double te = (v_ij * k.gb) * fma(0.5, visc_ec, o.PrRho);
     if (UM) { accA += ta; accE += te; }
     else { accA = fma(mj, ta, accA); accE = fma(mj, te, accE); }
-    return true;
 }
 
 // Shared-memory image of a tile and its surroundings for the force pass.
@@ -567,10 +598,11 @@ __device__ __forceinline__ bool sees_new_state(unsigned idxj, unsigned idxi) {
     return true;
 }
 
-// All neighbours on one side (DIR = -1: left, x_j <= x_i; +1: right) of particle `o`, staged part
-// first, then (rarely) global memory.  gradW carries sign(x_i - x_j) (calculators.cpp:17-27): the
-// unsigned sums of this side enter a with -DIR... i.e. a -= accA on the left, a += accA on the right,
-// and du/dt with the opposite signs.  `jend` receives the farthest slot within reach.
+// All neighbours on one side (DIR = -1: left, x_j <= x_i; +1: right) of particle `o`, summed from the
+// FARTHEST one inwards (the order in which the serial sweep meets them): first the extent of the scan is
+// found, then the pairs are evaluated on the way back.  gradW carries sign(x_i - x_j)
+// (calculators.cpp:17-27): the unsigned sums of this side enter a with -DIR... i.e. a -= accA on the left,
+// a += accA on the right, and du/dt with the opposite signs.  `jend` receives the farthest slot within reach.
 // SPLIT (refinement): a_sum / e_sum receive this side's unsigned sums instead of being merged, and `dyn` tells
 // whether the side holds a neighbour whose value can change while the tile iterates (seen in its new state and
 // inside the tile [dyn_lo, dyn_hi) of the staged window): a side without one need not be recomputed.
@@ -582,50 +614,63 @@ __device__ __forceinline__ void force_side(const SweepArgs &A, const ForceSmem &
     const double *sx = S.x + 1;
     const double dir = DIR > 0 ? -1.0 : 1.0;      // sign of x_i - x_j
     double accA = 0.0, accE = 0.0;
-    int k = ks + DIR;
+    // how far the scan goes inside the staged window: up to the first particle beyond reach_win (or a sentinel)
+    int kend = ks + DIR;
 #pragma unroll 1
-    while (true) {
+    while ((DIR > 0 ? (sx[kend] - o.x) : (o.x - sx[kend])) < reach_win) kend += DIR;
+    int jfar = wbase + kend - DIR;                // farthest slot within reach so far (ks itself if none)
+    // Inside the staged window no particle has a larger h than reach_win / 2.5, so whatever lies beyond the
+    // point where the scan stopped cannot interact.  BEYOND the window only the global bound is known: if it
+    // reaches past the outermost staged particle, the scan goes on from there in global memory (rare: it takes
+    // an h several times the local one, or more than kFHalo neighbours on one side) — those are the farthest
+    // neighbours, so they are summed first.
+    const double dist_end = DIR > 0 ? (sx[wn - 1] - o.x) : (o.x - sx[0]);
+    // (the global bound is re-read here rather than kept in registers through the loops)
+    const double reach = kRadius * __longlong_as_double(*((volatile long long *)&A.ctl->hmax_bits));
+    if (dist_end < reach) {
+        const int jstart = DIR > 0 ? wbase + wn : wbase - 1;
+        int j = jstart;
+#pragma unroll 1
+        for (; j >= lo && j < hi; j += DIR) {
+            const double xj = __ldg(A.F.x + j);
+            if (!((DIR > 0 ? (xj - o.x) : (o.x - xj)) < reach)) break;
+        }
+        if ((j < lo || j >= hi) && (DIR < 0 ? A.ctl->halo_left : A.ctl->halo_right)) raise(A.ctl, E_HALO, wbase + ks);
+        if (j != jstart) jfar = j - DIR;
+#pragma unroll 1
+        for (int q = j - DIR; DIR > 0 ? q >= jstart : q <= jstart; q -= DIR) {
+            const double xj = __ldg(A.F.x + q);
+            const double ar = DIR > 0 ? (xj - o.x) : (o.x - xj);
+            const bool useA = sees_new_state<SEL>(__ldg(A.F.idx + q), o.idx);
+            const Rec rj = useA ? A.F.rec[q].A : A.F.rec[q].B;
+            PairK pk;
+            if (pair_geom<ADIA>(o, ar, dir, rj, pk)) {
+                const double vj = (useA && !FIRST) ? ldv<true>(A.F.vA + q) : __ldg(A.F.vB + q);
+                const double uj = (useA && !FIRST) ? ldv<true>(A.F.uA + q) : __ldg(A.F.uB + q);
+                pair_apply<ADIA, UM>(o, pk, vj, uj, UM ? 0.0 : __ldg(A.F.m + q), accA, accE);
+                npairs++;
+            }
+        }
+    }
+    // the staged part, inwards
+#pragma unroll 1
+    for (int k = kend - DIR; k != ks; k -= DIR) {
         const double ar = DIR > 0 ? (sx[k] - o.x) : (o.x - sx[k]);
-        if (!(ar < reach_win)) break;             // also the +-INF sentinels
         const bool useA = sees_new_state<SEL>(S.idx[k], o.idx);
         const int sel = useA ? 0 : 1;
         const double2 hc = S.hc[sel][k], rk = S.rk[sel][k];
         Rec rj;
         rj.h = hc.x; rj.c5 = hc.y; rj.rho = rk.x; rj.kap = rk.y;
-        const double vj = (useA && !FIRST) ? S.vA[k] : S.vB[k];
-        const double uj = (useA && !FIRST) ? S.uA[k] : S.uB[k];
-        const double mj = UM ? 0.0 : __ldg(A.F.m + wbase + k);
-        if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) {
+        PairK pk;
+        if (pair_geom<ADIA>(o, ar, dir, rj, pk)) {
+            const double vj = (useA && !FIRST) ? S.vA[k] : S.vB[k];
+            const double uj = (useA && !FIRST) ? S.uA[k] : S.uB[k];
+            pair_apply<ADIA, UM>(o, pk, vj, uj, UM ? 0.0 : __ldg(A.F.m + wbase + k), accA, accE);
             npairs++;
             if (SPLIT && useA && k >= dyn_lo && k < dyn_hi) *dyn = true;
         }
-        k += DIR;
     }
-    // Inside the staged window no particle has a larger h than reach_win / 2.5, so whatever lies beyond the
-    // point where the scan stopped cannot interact.  BEYOND the window only the global bound is known: if it
-    // reaches past the outermost staged particle, go on from there in global memory (rare: it takes an h
-    // several times the local one, or more than kFHalo neighbours on one side).
-    int j = wbase + k;                            // first particle not handled above
-    const double dist_end = DIR > 0 ? (sx[wn - 1] - o.x) : (o.x - sx[0]);
-    // (the global bound is re-read here rather than kept in registers through the loop above)
-    const double reach = kRadius * __longlong_as_double(*((volatile long long *)&A.ctl->hmax_bits));
-    if (dist_end < reach) {
-        j = DIR > 0 ? wbase + wn : wbase - 1;
-#pragma unroll 1
-        for (; j >= lo && j < hi; j += DIR) {
-            const double xj = __ldg(A.F.x + j);
-            const double ar = DIR > 0 ? (xj - o.x) : (o.x - xj);
-            if (!(ar < reach)) break;
-            const bool useA = sees_new_state<SEL>(__ldg(A.F.idx + j), o.idx);
-            const Rec rj = useA ? A.F.rec[j].A : A.F.rec[j].B;
-            const double vj = (useA && !FIRST) ? ldv<true>(A.F.vA + j) : __ldg(A.F.vB + j);
-            const double uj = (useA && !FIRST) ? ldv<true>(A.F.uA + j) : __ldg(A.F.uB + j);
-            const double mj = UM ? 0.0 : __ldg(A.F.m + j);
-            if (pair_terms<ADIA, UM>(o, ar, dir, rj, vj, uj, mj, accA, accE)) npairs++;
-        }
-    }
-    if ((j < lo || j >= hi) && (DIR < 0 ? A.ctl->halo_left : A.ctl->halo_right)) raise(A.ctl, E_HALO, wbase + ks);
-    jend = j - DIR;
+    jend = jfar;
     if (SPLIT) {
         a_sum = accA;
         e_sum = accE;
@@ -873,6 +918,282 @@ __global__ void __launch_bounds__(kTile, 3) k_force_refine(SweepArgs A, int max_
     }
     if (blockIdx.x == 0 && threadIdx.x == 0 && peak > ctl->nwork_peak) ctl->nwork_peak = peak;
     if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->sweeps_used = used; ctl->epoch_cur = epoch; }
+}
+
+// ------------------------------------------------------------------------------------
+// The ordered sweep in ONE pass (k_force_sweep).
+//
+// The reference's second loop (sph_simulation.cpp:94-107) is a recurrence along the array index: particle i needs
+// the fully kicked (v, u) of its lower-index neighbours.  With the array kept x-sorted and the index order equal
+// to the x order (always, except for the handful of particles that have overtaken a neighbour), "lower index"
+// means "to the left", a few slots away.  The particle set is cut into segments; a GROUP of G lanes walks one
+// segment from left to right in chunks of G particles:
+//
+//   phase P (lanes in parallel, lane = particle): the right-hand neighbours (seen in their old state, known),
+//           the left-hand neighbours in earlier chunks (final values known), and for the left-hand neighbours
+//           INSIDE the chunk everything that does not depend on their kicked values (pair_geom);
+//   phase S (the chain): for t = 0 .. G-1 lane t's sums are complete, it is kicked, its (v, u) are broadcast,
+//           and the lanes to its right that see it add the pair (pair_apply, a dozen operations).
+//
+// A segment does not know the final values of the particles to its left.  It starts B particles early
+// ("burn-in") from nothing and discards what it computes there: the influence of a wrong left boundary decays
+// by an order of magnitude per neighbour hop, so after a few dozen particles the values are the exact ones.
+// "Are" is checked, not assumed: the burn-in results for the last G-1 particles before the segment are kept
+// (K.scr) and compared BIT FOR BIT with what the left segment stored for them (k_sweep_verify).  By induction
+// over the index every stored value is then the sequential sweep's.  Whatever this pass cannot settle —
+// a failed comparison, a neighbourhood wider than the G-1 slots a group looks back / ahead (judged with the
+// largest h of the surrounding tiles, `thm`), a right-hand neighbour with a lower index — queues the tile for
+// the work-list refinement (k_force_refine), which re-evaluates it from the stored values, propagates any change,
+// and reaches the same fixed point.  Both kernels evaluate a particle with the same functions in the same
+// order, so an unflagged particle passes that evaluation unchanged.
+constexpr int kSweepThreads = 128;
+
+struct SerialArgs {
+    SweepArgs S;
+    const unsigned *thm;   // per tile of kTile slots: largest h (float bits, rounded up), from the density pass
+    int nthm;              // tiles in thm
+    double *scr;           // [nseg][2][G-1]: burn-in results next to the segment start, for k_sweep_verify
+    int L, B, nseg;        // segment length, burn-in length (multiples of G), number of segments
+};
+
+template <int G>
+struct SweepGrp {          // shared memory of one group: three chunks of particle records + the pair constants of a chunk
+    static constexpr int W = 3 * G, NK = G * (G - 1) / 2;
+    double2 hcA[W], rkA[W], hcB[W], rkB[W];   // (h, c5), (rho, kap) of the new (A) and the old (B) state
+    double x[W], vB[W], uB[W], vA[W], uA[W];
+    double kc[4][NK];      // PairK of lane l's pair with lane t < l at [t (G-1) - t (t-1)/2 + l - t - 1]
+    unsigned idx[W];
+};
+
+__device__ __forceinline__ void queue_tile(const SweepArgs &A, int t, int epoch) {
+    if (atomicMax(A.dirty + t, epoch) < epoch) {
+        const int slot = atomicAdd(&A.ctl->nwork[(epoch + 1) % 3], 1);
+        A.wl[(epoch + 1) % 3][slot] = t;
+    }
+}
+
+template <bool ADIA, int G>
+__global__ void __launch_bounds__(kSweepThreads, G == 8 ? 4 : 3) k_force_sweep(SerialArgs K) {
+    constexpr int R = G - 1;
+    using Grp = SweepGrp<G>;
+    extern __shared__ __align__(16) unsigned char sweep_smem[];
+    const SweepArgs &A = K.S;
+    Ctl *ctl = A.ctl;
+    const int gl = threadIdx.x % G;                  // lane within the group
+    const int grp = threadIdx.x / G;
+    const int seg = blockIdx.x * (kSweepThreads / G) + grp;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->epoch_cur = A.epoch; ctl->sweeps_used = 1; }
+    if (seg >= K.nseg) return;                       // whole groups leave together
+    Grp &S = reinterpret_cast<Grp *>(sweep_smem)[grp];
+    const unsigned gmask = ((G == 32) ? 0xffffffffu : ((1u << G) - 1u)) << (((threadIdx.x & 31) / G) * G);
+    const int lo = A.pad - ctl->GL, hi = A.pad + A.na + ctl->GR;
+    const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
+    const double reach_glob = kRadius * Hb;
+    const int seg_lo = A.pad + seg * K.L, seg_hi = min(seg_lo + K.L, A.pad + A.na);
+    const int st = (seg == 0) ? lo : max(lo, seg_lo - K.B);   // first slot this group looks at
+    const int nch = (seg_hi - st + G - 1) / G;
+    const bool halo_l = ctl->halo_left != 0, halo_r = ctl->halo_right != 0;
+
+    struct Pre { double x, vB, uB, gs, pst; double2 hcA, rkA, hcB, rkB; unsigned idx; };
+    auto fetch = [&](int c) -> Pre {
+        Pre p;
+        const int s = st + c * G + gl;
+        if (s >= lo && s < hi) {
+            p.x = A.F.x[s]; p.idx = A.F.idx[s];
+            const double2 *r = reinterpret_cast<const double2 *>(A.F.rec + s);
+            p.hcA = r[0]; p.rkA = r[1]; p.hcB = r[2]; p.rkB = r[3];
+            p.vB = A.F.vB[s]; p.uB = A.F.uB[s];
+            p.gs = A.F.gsum[s]; p.pst = A.Pstale[s];
+        } else {
+            p.x = s < lo ? -INFINITY : INFINITY; p.idx = 0xffffffffu;
+            p.hcA = p.rkA = p.hcB = p.rkB = make_double2(0.0, 0.0);
+            p.vB = p.uB = p.gs = p.pst = 0.0;
+        }
+        return p;
+    };
+    auto put = [&](int buf, const Pre &p) {
+        const int q = buf * G + gl;
+        S.x[q] = p.x; S.idx[q] = p.idx; S.hcA[q] = p.hcA; S.rkA[q] = p.rkA; S.hcB[q] = p.hcB; S.rkB[q] = p.rkB;
+        S.vB[q] = p.vB; S.uB[q] = p.uB; S.vA[q] = p.vB; S.uA[q] = p.uB;
+    };
+    double gs_c, pst_c, gs_n, pst_n;
+    {
+        const Pre p0 = fetch(0), p1 = fetch(1);
+        put(0, p0); put(1, p1);
+        Pre none;                                    // "chunk -1": nothing to the left of the start
+        none.x = -INFINITY; none.idx = 0xffffffffu;
+        none.hcA = none.rkA = none.hcB = none.rkB = make_double2(0.0, 0.0);
+        none.vB = none.uB = none.gs = none.pst = 0.0;
+        put(2, none);
+        gs_c = p0.gs; pst_c = p0.pst; gs_n = p1.gs; pst_n = p1.pst;
+    }
+    __syncwarp(gmask);
+    int npairs_tot = 0, nmoved = 0, nflag = 0;
+
+#pragma unroll 1
+    for (int c = 0; c < nch; c++) {
+        const int bc = c % 3, bp = (c + 2) % 3, bn = (c + 1) % 3;
+        const Pre nx = fetch(c + 2);                 // replaces chunk c - 1 once phase P is done with it
+        const int s = st + c * G + gl;
+        const int me = bc * G + gl;
+        const unsigned idxi = S.idx[me];
+        const bool eval = s < seg_hi && !(idxi & kGhostBit);   // alive (own or a neighbouring slab's); free slots carry 0xffffffff
+        const bool store = eval && s >= seg_lo;
+        const double vi = S.vB[me], ui = S.uB[me];
+        Own<ADIA> o;
+        {
+            Rec ro;
+            ro.h = S.hcA[me].x; ro.c5 = S.hcA[me].y; ro.rho = S.rkA[me].x; ro.kap = S.rkA[me].y;
+            o.set(S.x[me], idxi, ro, vi, ui, pst_c);
+        }
+        double aL = 0.0, eL = 0.0, aR = 0.0, eR = 0.0;
+        unsigned vmask = 0u, dmask = 0u;
+        bool flag = false;
+        if (eval) {
+            // the scan bound: 2.5 x the largest h of the three tiles around this particle, never above the global one
+            const int tl = s / kTile;
+            unsigned hb = K.thm[tl];
+            if (tl > 0) hb = max(hb, K.thm[tl - 1]);
+            if (tl + 1 < K.nthm) hb = max(hb, K.thm[tl + 1]);
+            const double reach_loc = fmin(reach_glob, kRadius * (double)__uint_as_float(hb));
+            // slot s + q, -G <= q < 2G, in the ring
+            auto rpos = [&](int q) { const int p = gl + q; return p < 0 ? bp * G + p + G : (p < G ? bc * G + p : bn * G + p - G); };
+            int dL = 0, dR = 0;                      // candidates per side; G = more than a group can hold
+#pragma unroll 1
+            while (dL < G && (o.x - S.x[rpos(-(dL + 1))]) < reach_loc) dL++;
+#pragma unroll 1
+            while (dR < G && (S.x[rpos(dR + 1)] - o.x) < reach_loc) dR++;
+            if (store) {
+                if (dL == G || dR == G) flag = true;
+                // the scan stopped at the end of the array, not at a particle out of reach: next to a wall that is
+                // the end of the world, on a slab edge the halo is thinner than the kernel reaches
+                if ((dL < G && s - (dL + 1) < lo && halo_l) || (dR < G && s + dR + 1 >= hi && halo_r)) raise(ctl, E_HALO, s);
+                // tiles further away than the neighbouring one are only covered by the global bound
+                const int fl = (tl - 1) * kTile, fr = (tl + 2) * kTile - 1;
+                if (fl > lo && (o.x - __ldg(A.F.x + fl)) < reach_glob) flag = true;
+                if (fr < hi - 1 && (__ldg(A.F.x + fr) - o.x) < reach_glob) flag = true;
+            }
+            dL = min(dL, R); dR = min(dR, R);
+            npairs_tot++;                            // self: its energy term is evaluated by the reference too (and is exactly 0)
+            // left-hand side, farthest first
+#pragma unroll 1
+            for (int d = dL; d >= 1; d--) {
+                const int p = gl - d;
+                const int rp = p < 0 ? bp * G + p + G : bc * G + p;
+                const bool useA = S.idx[rp] < o.idx;             // the reference's sweep has already updated j
+                const double2 hc = useA ? S.hcA[rp] : S.hcB[rp], rk = useA ? S.rkA[rp] : S.rkB[rp];
+                Rec rj;
+                rj.h = hc.x; rj.c5 = hc.y; rj.rho = rk.x; rj.kap = rk.y;
+                PairK pk;
+                if (!pair_geom<ADIA>(o, o.x - S.x[rp], 1.0, rj, pk)) continue;
+                npairs_tot++;
+                if (p < 0) {                                     // an earlier chunk: its final values are in the ring
+                    pair_apply<ADIA, true>(o, pk, useA ? S.vA[rp] : S.vB[rp], useA ? S.uA[rp] : S.uB[rp], 0.0, aL, eL);
+                } else {
+                    const int q = p * R - (p * (p - 1)) / 2 + (gl - p - 1);
+                    if (useA) {                                  // this chunk: added when lane p has been kicked
+                        S.kc[0][q] = pk.K2; S.kc[1][q] = pk.irho; S.kc[2][q] = pk.gb; S.kc[3][q] = pk.G1;
+                        vmask |= 1u << p;
+                    } else {                                     // a ghost, or a higher index: seen in its old state
+                        double ta = 0.0, te = 0.0;
+                        pair_apply<ADIA, true>(o, pk, S.vB[rp], S.uB[rp], 0.0, ta, te);
+                        S.kc[0][q] = ta; S.kc[1][q] = te;
+                        dmask |= 1u << p;
+                    }
+                }
+            }
+            // right-hand side, farthest first: old state
+#pragma unroll 1
+            for (int d = dR; d >= 1; d--) {
+                const int p = gl + d;
+                const int rp = p < G ? bc * G + p : bn * G + p - G;
+                if (S.idx[rp] < o.idx) flag = true;              // overtaken: it is seen in its NEW state, which is not known yet
+                const double2 hc = S.hcB[rp], rk = S.rkB[rp];
+                Rec rj;
+                rj.h = hc.x; rj.c5 = hc.y; rj.rho = rk.x; rj.kap = rk.y;
+                PairK pk;
+                if (pair_geom<ADIA>(o, S.x[rp] - o.x, -1.0, rj, pk)) {
+                    pair_apply<ADIA, true>(o, pk, S.vB[rp], S.uB[rp], 0.0, aR, eR);
+                    npairs_tot++;
+                }
+            }
+        }
+        __syncwarp(gmask);                           // everybody is done with chunk c - 1
+        {
+            const int q = bp * G + gl;
+            S.x[q] = nx.x; S.idx[q] = nx.idx; S.hcA[q] = nx.hcA; S.rkA[q] = nx.rkA; S.hcB[q] = nx.hcB; S.rkB[q] = nx.rkB;
+            S.vB[q] = nx.vB; S.uB[q] = nx.uB; S.vA[q] = nx.vB; S.uA[q] = nx.uB;
+        }
+        // the chain
+        double my_a = 0.0, my_e = 0.0, my_vf = vi, my_uf = ui;
+#pragma unroll
+        for (int t = 0; t < G; t++) {
+            // merged exactly as the other force kernels merge them: (0 - left) + right, (0 + left) - right
+            double a_s = (0.0 - aL) + aR, e_s = (0.0 + eL) - eR;
+            a_s *= A.m0; e_s *= A.m0;
+            a_s = fma(-o.PrRho, gs_c, a_s);
+            // second half-kick, sph_simulation.cpp:105-106, operation by operation
+            const double vf = __dadd_rn(vi, __dmul_rn(a_s, A.half_dt));
+            const double uf = __dadd_rn(ui, __dmul_rn(e_s, A.half_dt));
+            if (gl == t) { my_a = a_s; my_e = e_s; my_vf = vf; my_uf = uf; }
+            const double bv = __shfl_sync(gmask, vf, t, G), bu = __shfl_sync(gmask, uf, t, G);
+            if (gl > t) {
+                const int q = t * R - (t * (t - 1)) / 2 + (gl - t - 1);
+                if ((vmask >> t) & 1u) {
+                    PairK pk;
+                    pk.K2 = S.kc[0][q]; pk.irho = S.kc[1][q]; pk.gb = S.kc[2][q]; pk.G1 = S.kc[3][q];
+                    pair_apply<ADIA, true>(o, pk, bv, bu, 0.0, aL, eL);
+                } else if ((dmask >> t) & 1u) {
+                    aL += S.kc[0][q]; eL += S.kc[1][q];
+                }
+            }
+        }
+        if (eval) { S.vA[me] = my_vf; S.uA[me] = my_uf; }
+        bool moved = false;
+        if (store) {
+            A.a[s] = my_a; A.du[s] = my_e; A.Pout[s] = o.P;
+            A.vn[s] = my_vf; A.un[s] = my_uf;
+            moved = __double_as_longlong(my_vf) != __double_as_longlong(vi) || __double_as_longlong(my_uf) != __double_as_longlong(ui);
+            if (flag) { queue_tile(A, (s - A.pad) / kTile, A.epoch); nflag++; }
+        } else if (eval) {
+            if (s < A.pad) {
+                // a neighbouring slab's particle: my estimate of its final values; the owner's arrive with the
+                // ITERATE message and are compared with these
+                A.vn[s] = my_vf; A.un[s] = my_uf;
+            } else if (s >= seg_lo - R) {
+                K.scr[(size_t)(2 * seg) * R + (s - (seg_lo - R))] = my_vf;
+                K.scr[(size_t)(2 * seg + 1) * R + (s - (seg_lo - R))] = my_uf;
+            }
+        }
+        if ((__ballot_sync(gmask, moved) & gmask) && gl == 0) nmoved++;
+        gs_c = gs_n; pst_c = pst_n; gs_n = nx.gs; pst_n = nx.pst;
+        __syncwarp(gmask);
+    }
+    // statistics: pairs for the roofline accounting, chunks with a non-zero kick, flagged particles
+    npairs_tot = __reduce_add_sync(gmask, npairs_tot);
+    nflag = __reduce_add_sync(gmask, nflag);
+    if (gl == 0) {
+        atomicAdd(&ctl->force_pairs[seg % kStatBins], (unsigned long long)npairs_tot);
+        if (nmoved) atomicAdd(&ctl->sweep_moved_chunks, nmoved);
+        if (nflag) atomicAdd(&ctl->sweep_flagged, nflag);
+    }
+}
+
+// Burn-in check of the serial sweep: what segment `seg` computed for the R particles before its first one must
+// be, bit for bit, what the segment to its left stored for them.  If not, the segment's first tile is
+// re-evaluated by the work-list refinement (which passes any change on to the right).
+__global__ void k_sweep_verify(SerialArgs K, int R) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int seg = 1 + t / R, r = t % R;
+    if (seg >= K.nseg) return;
+    const SweepArgs &A = K.S;
+    const int seg_lo = A.pad + seg * K.L;
+    const int s = seg_lo - R + r;
+    const double v = K.scr[(size_t)(2 * seg) * R + r], u = K.scr[(size_t)(2 * seg + 1) * R + r];
+    if (__double_as_longlong(v) != __double_as_longlong(A.vn[s]) || __double_as_longlong(u) != __double_as_longlong(A.un[s])) {
+        atomicAdd(&A.ctl->sweep_verify_fail, 1);
+        queue_tile(A, (seg_lo - A.pad) / kTile, A.ctl->epoch_cur);
+    }
 }
 
 // ------------------------------------------------------------------------------------
@@ -1461,6 +1782,9 @@ __global__ void k_begin(Ctl *ctl, int clear_cand) {
     ctl->tile_evals = 0;
     ctl->tiles_swept = 0;
     ctl->halo_changed = 0;
+    ctl->sweep_flagged = 0;
+    ctl->sweep_verify_fail = 0;
+    ctl->sweep_moved_chunks = 0;
     for (int b = 0; b < kStatBins; b++) { ctl->force_pairs[b] = 0ull; ctl->density_scans[b] = 0ull; }
 }
 
