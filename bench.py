@@ -38,20 +38,24 @@ if ROOT not in sys.path:
 METRIC = "particle_steps_per_sec"
 UNIT = "particle-steps/s"
 
-# name -> (N, pressure_calc, variable_h); h for fixed-h runs is 5 lattice spacings
+# name -> (N, pressure_calc, variable_h); h for fixed-h runs is 5 lattice spacings.
+# Decimal particle counts are the default family: their lattice positions are not exactly equidistant in floating
+# point, so every particle of the undisturbed streams feels a rounding-level kick and the index-ordered sweep has
+# work EVERYWHERE, as it has in any developed flow.  With N = 2^k the positions are dyadic, the undisturbed streams
+# feel |a| ~ 1e-13 and only the ~100 tiles around the collision front and the walls are re-swept: those workloads
+# are kept as the labelled best case ("..._pow2").
 WORKLOADS = {
-    "colliding_streams_adiabatic_varh_n64m": (64 * 1024 * 1024, 1, True),     # BASELINE configs[3], the target line
-    "colliding_streams_adiabatic_varh_n16m": (16 * 1024 * 1024, 1, True),     # configs[2]
-    "colliding_streams_isothermal_fixedh_n1m": (1024 * 1024, 0, False),       # configs[1]
-    "colliding_streams_adiabatic_varh_n256m": (256 * 1024 * 1024, 1, True),   # configs[4]
-    "colliding_streams_adiabatic_varh_n1m": (1024 * 1024, 1, True),
-    # generic particle counts: the lattice positions are not exactly equidistant in floating point, so every
-    # particle of the undisturbed streams feels a rounding-level kick and the ordered sweep has work everywhere
-    "colliding_streams_adiabatic_varh_n64000000": (64_000_000, 1, True),
-    "colliding_streams_adiabatic_varh_n16000000": (16_000_000, 1, True),
-    "colliding_streams_isothermal_fixedh_n1000000": (1_000_000, 0, False),
+    "colliding_streams_adiabatic_varh_n64m": (64_000_000, 1, True),           # BASELINE configs[3], the target line
+    "colliding_streams_adiabatic_varh_n16m": (16_000_000, 1, True),           # configs[2]
+    "colliding_streams_isothermal_fixedh_n1m": (1_000_000, 0, False),         # configs[1]
+    "colliding_streams_adiabatic_varh_n256m": (256_000_000, 1, True),         # configs[4]: per GPU with --scaling weak
+    "colliding_streams_adiabatic_varh_n1m": (1_000_000, 1, True),
+    "colliding_streams_adiabatic_varh_n64m_pow2": (64 * 1024 * 1024, 1, True),    # best case of the ordered sweep
+    "colliding_streams_adiabatic_varh_n16m_pow2": (16 * 1024 * 1024, 1, True),
+    "colliding_streams_isothermal_fixedh_n1m_pow2": (1024 * 1024, 0, False),
 }
 DEFAULT_WORKLOAD = "colliding_streams_adiabatic_varh_n64m"
+FP64_ROOF_TFLOPS = 37.2    # assumed: 148 SMs x 64 FP64 lanes x 2 flop x 1.965 GHz (MEASURED_PEAKS.json has no FP64 figure)
 
 
 def workload_kwargs(n, pc, varh):
@@ -84,7 +88,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                 "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "10"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thr = threading.Thread(target=self._pump, daemon=True)
             self.thr.start()
         except Exception:
@@ -171,21 +175,28 @@ def run_reference(args, name, n_full, pc, varh):
             wall = time.perf_counter() - t0
         dt = max(dts)
         value = cores * n_s * steps_s / dt
+        single = n_s * steps_s / min(dts)
         kind = "reference"
-        sample = ("reference sources compiled unmodified (-Ofast), %d independent replicas (one per core) of the same "
-                  "lattice at N=%d, %d steps each, slowest replica %.2f s (wall %.1f s); the reference step is O(N^%d) so "
-                  "its rate falls as N grows" % (cores, n_s, steps_s, dt, wall, 3 if varh else 2))
+        sample = ("reference sources compiled unmodified (-Ofast), %d independent single-threaded replicas (one per host core) of "
+                  "the same lattice at N=%d, %d steps each, slowest replica %.2f s (wall %.1f s); value = sum over replicas, "
+                  "single_replica_value = one of them; the reference step is O(N^%d), so its rate falls as N grows and N=%d "
+                  "is the largest sample that keeps this arm within minutes" % (cores, n_s, steps_s, dt, wall, 3 if varh else 2, n_s))
         ms = dt / steps_s * 1e3
         steps_out = steps_s
+        n_ran = n_s
     else:
         b = cpu_port_baseline(pc, varh)
         value, kind, sample, cores = b["value"], "port", b["sample"], 1
+        single = value
         ms, steps_out = None, 3
+        n_ran = 600_001
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": steps_out, "warmup": warm, "ms_per_step": ms, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": name, "n_particles": n_full},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+            "config": {"workload": name, "n_particles": n_ran, "n_particles_of_the_gpu_arm": n_full,
+                       "note": "the reference cannot run the GPU arm's N (O(N^3) per step): same generator, same physics, at the N named here"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
+                             "single_replica_value": single, "replicas": cores if kind == "reference" else 1},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -193,6 +204,45 @@ def run_reference(args, name, n_full, pc, varh):
 
 
 # ------------------------------------------------------------------------------------------
+
+def slab_parity(args, world, rank, local, n=200_001, steps=6):
+    """Evidence that the multi-GPU path computes the same thing: on the SAME ranks and NCCL transport as the timed run,
+    a small problem is advanced as x-slabs and, on every rank, as one single-GPU handle; every field of every particle
+    a rank owns must be bit-identical, and the all-reduced conservation totals must equal the single handle's."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from sph_b200 import Config, Simulation
+    from sph_b200.slabs import make_simulation
+    cfg = Config(n_part=n, mass=4.0 / (n - 1), pressure_calc=1, t_i=0.005 * 100 / (n - 1))
+    one = Simulation(cfg, device=local, sweep_mode=args.sweep_mode)
+    one.init_lattice()
+    sl = make_simulation(cfg, device=local, rank=rank, world=world, halo_count=128, native=not args.torch_exchange,
+                         sweep_mode=args.sweep_mode)
+    sl.init_lattice()
+    bad = 0
+    for st in range(steps + 1):
+        if st:
+            one.step(1)
+            sl.step(1)
+        if st in (0, 1, steps):
+            f1 = one.fields()[0]
+            f2, _, _, ids = sl.fields()
+            bad += 0 if np.array_equal(f1[ids], f2[:len(ids)]) else 1
+    d1 = one.diagnostics()
+    d2 = sl.ranks[0].diagnostics()
+    t = torch.tensor([float(bad), d2["mass"], d2["momentum"], d2["kinetic"], d2["thermal"]], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t)
+    tot = dict(mass=float(t[1]), momentum=float(t[2]), kinetic=float(t[3]), thermal=float(t[4]))
+    rel = max(abs(tot[k] - d1[k]) / max(abs(d1[k]), 1e-30) for k in ("mass", "kinetic", "thermal"))
+    serial_steps = sl.counters().sweep_steps
+    sl.close()
+    one.close()
+    ok = int(t[0].item()) == 0 and rel < 1e-12
+    return {"verdict": "identical" if ok else "differs", "n_particles": n, "steps": steps, "ranks_with_a_difference": int(t[0].item()),
+            "totals_all_reduced": tot, "totals_single_gpu": d1, "totals_max_rel_diff": rel, "serial_sweep_steps": serial_steps,
+            "compared": "every field of every owned particle at steps 0, 1, %d, bit for bit, on each rank" % steps}
+
 
 def run_ours(args, name, n, pc, varh):
     import numpy as np
@@ -212,6 +262,8 @@ def run_ours(args, name, n, pc, varh):
         if world == 1 and args.gpus > 1:
             raise SystemExit("bench.py --gpus %d must be launched under torch.distributed.run" % args.gpus)
 
+    if args.scaling == "weak":
+        n = n * world            # the named N is per GPU; 8 x 256,000,000 stays below 2^31 (the index field)
     kw = workload_kwargs(n, pc, varh)
     cfg = Config(n_part=n, mass=kw["mass"], pressure_calc=pc, t_i=kw["t_i"])
     from sph_b200.slabs import make_simulation   # 1 rank: a plain Simulation; >1: this rank's x-slab
@@ -285,13 +337,19 @@ def run_ours(args, name, n, pc, varh):
     # neighbour-window scans actually made per particle (1 + Newton iterations, minus the last one wherever the
     # final Newton step was below 1e-12 and the previous sums were reused)
     passes = c2.density_scans_mean if c2.density_scans_mean > 0 else ((1.0 + newton_mean) if varh else 1.0)
-    # algorithmic bytes per particle: density kernel reads x,h,rho and writes
-    # h,rho,omega_new,omega_stale (56 B) + 8 B (x_j) per neighbour per pass of the root-find
+    # Bytes per particle-step.  SURVEY 8(d)'s figure B_ns counts every neighbour read ("bytes touched per particle x
+    # neighbours"): density 56 + 8 B (x_j) per neighbour per pass of the root-find, force 124 + 56 B per pair, kick 64.
+    # The kernels serve neighbours from shared memory, so what can actually cross the HBM interface is the
+    # COMPULSORY traffic: density reads x, h, rho (24 B) and writes h, rho, the two force records, the gradient sum
+    # and the packed counts (92 B) = 116 B; the force kernel reads x, idx, both records, v, u, gradient sum, stored
+    # pressure (108 B) and writes a, du/dt, P, v, u (40 B) = 148 B; kick-drift 72 B.  roofline.frac uses those
+    # (ncu's dram__bytes, `traffic`, agree with them); the B_ns figures are reported beside it, not as the fraction.
     bytes_density = (56.0 if varh else 24.0) + 8.0 * passes * nbr_rho
     rec = 56.0 if varh else 40.0
     bytes_force = (124.0 if pc == 1 else 92.0) + rec * nbr_f
     bytes_kick = 64.0
     b_ns = bytes_kick + bytes_density + bytes_force
+    comp = {"density": 116.0, "force_first": 148.0, "kick_drift": 72.0}
     peak, peak_src = measured_peaks()
     d_ms = phases["density"][0] / max(phases["density"][1], 1)
     f_ms = phases["force_first"][0] / max(phases["force_first"][1], 1)
@@ -299,26 +357,36 @@ def run_ours(args, name, n, pc, varh):
     k_ms = phases["kick_drift"][0] / max(phases["kick_drift"][1], 1)
     step_prof_ms = sum(v[0] for v in phases.values()) / prof_steps
     dom = max((("density", d_ms, bytes_density), ("force_first", f_ms, bytes_force)), key=lambda t: t[1])
-    achieved = n_local * dom[2] / (dom[1] * 1e-3) / 1e9 if dom[1] > 0 else 0.0
-    kname = "k_density" if dom[0] == "density" else "k_force_first"
-    traffic = None
-    try:   # dram bytes per launch from the committed ncu --set full capture, scaled to this launch's particles
-        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic_r01.json")))
-        traffic = (tr[kname]["dram_bytes_read"] + tr[kname]["dram_bytes_write"]) / tr["n_particles"] * n_local
-    except Exception:
-        pass
+    serial = c2.sweep_group > 0
+    kname = "k_density" if dom[0] == "density" else ("k_force_sweep" if serial else "k_force_first")
+    achieved = n_local * comp[dom[0]] / (dom[1] * 1e-3) / 1e9 if dom[1] > 0 else 0.0
+    achieved_b_ns = n_local * dom[2] / (dom[1] * 1e-3) / 1e9 if dom[1] > 0 else 0.0
+    traffic = fp64_pct = None
+    tsrc = None
+    for tf in ("traffic_r02.json", "traffic_r01.json"):
+        try:   # per launch, from the committed ncu --set full capture, scaled per particle to this launch
+            tr = json.load(open(os.path.join(ROOT, "profiles", tf)))
+            traffic = (tr[kname]["dram_bytes_read"] + tr[kname]["dram_bytes_write"]) / tr[kname].get("n_particles", tr.get("n_particles")) * n_local
+            fp64_pct = tr[kname].get("fp64_pipe_pct")
+            tsrc = "profiles/%s: %s" % (tf, tr.get("source", ""))
+            break
+        except Exception:
+            continue
     roofline = {"bound": "hbm", "kernel": kname,
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "profiles/traffic_r01.json: ncu dram__bytes_read+write per launch at N = 64 Mi (--set full), scaled per particle",
-                "peak_source": peak_src, "bytes_per_particle": dom[2], "launch_ms": dom[1],
-                "compulsory_bytes_per_particle": (148.0 if dom[0] != "density" else 116.0),
-                "frac_compulsory": (n_local * (148.0 if dom[0] != "density" else 116.0) / (dom[1] * 1e-3) / 1e9 / peak) if dom[1] > 0 else None,
-                "note": "algorithmic bytes count every neighbour read (SURVEY 8d) although tiles serve them from shared memory; "
-                        "ncu: both hot kernels move their compulsory bytes once and are limited by the half-rate FP64 pipe and "
-                        "instruction issue (profiles/r01_summary.md)",
-                "step_b_ns_bytes_per_particle": b_ns,
-                "step_frac_b_ns": value / world * b_ns / 1e9 / peak,
-                "step_frac_compulsory_244B": value / world * (244.0 if varh else 156.0) / 1e9 / peak,
+                "traffic_source": tsrc, "peak_source": peak_src,
+                "bytes_per_particle": comp[dom[0]], "launch_ms": dom[1],
+                "bytes_basis": "compulsory HBM traffic of the kernel (inputs read once + outputs written once); "
+                               "neighbour reads are served from shared memory",
+                "fp64_pipe_frac": (fp64_pct / 100.0) if fp64_pct is not None else None,
+                "fp64_roof_tflops_assumed": FP64_ROOF_TFLOPS,
+                "note": "the kernel sits between the roofs: it moves its compulsory bytes once (traffic ~ bytes_per_particle x N) and "
+                        "is limited by dependent FP64 chains / instruction issue, not by HBM (profiles/r02_summary.md)",
+                "survey_b_ns": {"bytes_per_particle_kernel": dom[2], "achieved_kernel_gbs": achieved_b_ns,
+                                "frac_kernel": achieved_b_ns / peak,
+                                "bytes_per_particle_step": b_ns, "frac_step": value / world * b_ns / 1e9 / peak,
+                                "note": "SURVEY 8(d) formula: counts every neighbour read as HBM traffic, can exceed 1; not the roofline fraction"},
+                "step_frac_compulsory": value / world * ((116.0 + 148.0 + 72.0)) / 1e9 / peak,
                 "phase_ms": {"kick_drift": k_ms, "density": d_ms, "force_first": f_ms, "force_refine": r_ms,
                              "sort": phases["sort"][0] / prof_steps, "ghosts": phases["ghosts"][0] / prof_steps,
                              "step_sum": step_prof_ms},
@@ -332,7 +400,10 @@ def run_ours(args, name, n, pc, varh):
         hs = sim if world == 1 else sim.ranks[0]     # the object that owns this rank's handle
         n_loc = n_local
         nbuf = n_loc + 2 * 4096
-        host = torch.empty(nbuf * PARTICLE_DTYPE.itemsize, dtype=torch.uint8, pin_memory=True)
+        try:
+            host = torch.empty(nbuf * PARTICLE_DTYPE.itemsize, dtype=torch.uint8, pin_memory=True)
+        except RuntimeError:     # the box cannot pin that much host memory: pageable buffers (slower copies)
+            host = torch.empty(nbuf * PARTICLE_DTYPE.itemsize, dtype=torch.uint8)
         rec_arr = host.numpy().view(PARTICLE_DTYPE)
         out, ng = hs.download(rec_arr)
         barrier()
@@ -362,6 +433,8 @@ def run_ours(args, name, n, pc, varh):
     rounds_last = getattr(sim, 'rounds_last', 0)
     sim.close()
 
+    parity = slab_parity(args, world, rank, local) if world > 1 else None
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_port_baseline(pc, varh)
@@ -372,12 +445,16 @@ def run_ours(args, name, n, pc, varh):
     if rank != 0:
         return 0
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": name, "n_particles": n, "pressure_calc": "adiabatic" if pc == 1 else "isothermal",
                        "smoothing_length": "variable (Newton/bisection per particle)" if varh else "fixed, 5 spacings",
+                       "lattice": ("N = 2^k: dyadic positions, undisturbed streams feel no kick: best case of the ordered sweep"
+                                   if (n // world if args.scaling == "weak" else n) & ((n // world if args.scaling == "weak" else n) - 1) == 0
+                                   else "generic N: every particle feels a rounding-level kick, the ordered sweep has work everywhere"),
                        "order": ("reference (index-ordered in-place sweep, bitwise fixed point)" if args.sweep_tol == 0 else
                                  "reference (index-ordered in-place sweep, converged to %.1e relative)" % args.sweep_tol), "sweeps_per_step": sweeps_mean,
+                       "n_particles_per_gpu": n // world,
                        "parallelism": ("x-slabs x%d, %d-particle halos over ncclSend/ncclRecv, %d ITERATE exchanges in the last step"
                                        % (world, args.halo, rounds_last)) if world > 1 else "single GPU",
                        "sweep": {"serial_steps": c2.sweep_steps, "group": c2.sweep_group, "segment": c2.sweep_segment,
@@ -385,6 +462,9 @@ def run_ours(args, name, n, pc, varh):
                                  "refine_tiles": c2.refine_tiles, "refine_tile_evals": c2.refine_tile_evals},
                        "l2": "state arrays (%.1f GB) larger than L2, no flush needed" % (n * 8 * 20 / 1e9)},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
+    if parity is not None:
+        line["slab_parity"] = parity["verdict"]
+        line["slab_parity_detail"] = parity
     print(json.dumps(line), flush=True)
     return 0
 
@@ -400,6 +480,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sweep-tol", type=float, default=0.0,
                     help="0 (default): the ordered sweep is iterated to its bitwise fixed point; > 0: relative tolerance")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="--gpus N > 1: strong = the named N in total, weak = the named N per GPU")
     ap.add_argument("--sweep-mode", type=int, default=0, help="ordered sweep: 0 auto, 1 work lists, 2 serial sweep")
     ap.add_argument("--sweep-group", type=int, default=0)
     ap.add_argument("--sweep-segment", type=int, default=0)

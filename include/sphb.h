@@ -196,8 +196,11 @@ int sphb_get_phase_times(sphb_handle *h, double *ms, long long *launches, int re
  * Step: step_begin | exchange BASE | density | exchange RECORDS | force_first, refine |
  *       { exchange ITERATE | refine } a fixed number of rounds | exchange ITERATE | poll (the step's one
  *       host synchronisation) | ranks agree on MAX(flags): error -> raise; order broken -> resort and
- *       repeat from 'exchange BASE'; halo changed -> more rounds; else step_end.                    */
+ *       repeat from 'exchange BASE'; halo changed -> more rounds; else agree (halo width), step_end.
+ * With the serial sweep (sphb_options.sweep_mode) force_first walks the slab once, the left halo included, and the
+ * ITERATE exchanges only confirm what it computed for the halo particles.                            */
 enum { SPHB_MSG_BASE = 0, SPHB_MSG_RECORDS = 1, SPHB_MSG_ITERATE = 2 };
+/* messages: BASE 8 rows, RECORDS 9 rows, ITERATE 2 rows of halo_count doubles, plus a header */
 /* this handle holds global particle indices [index_offset, index_offset + n_alive) of n_global;
  * halo_count particles travel per edge (must exceed the kernel reach in particles; too thin a halo is
  * detected on the device and reported as SPHB_ERR_HALO).  A particle that overtakes its neighbour across a
@@ -214,8 +217,11 @@ int sphb_slab_step_begin(sphb_handle *h);   /* kick-drift, order check (+ sort),
 int sphb_slab_density(sphb_handle *h);      /* density + root-find + omega + records of own particles */
 int sphb_slab_force_first(sphb_handle *h);  /* first force sweep + second kick */
 int sphb_slab_refine(sphb_handle *h);       /* ordered-sweep refinement until the local work list is empty */
-int sphb_slab_poll(sphb_handle *h, int *flags4);  /* {device error code, x-order broken, halo iterate changed, h max as float bits} */
-int sphb_slab_check_halo(sphb_handle *h, int hmax_float_bits);   /* with MAX over ranks of flags4[3]: do my halos cover it? */
+int sphb_slab_poll(sphb_handle *h, int *flags6);  /* {device error code, x-order broken, halo iterate changed, h max as float bits,
+                                                      thinner halo of this rank (coded so that MAX = thinnest), work lists busy} */
+/* with the element-wise MAX over ranks of the polled flags: does the widest kernel support of the run fit inside its thinnest
+ * halo (every rank gets the same answer, so all leave the step together), and the sweep strategy of the next step */
+int sphb_slab_agree(sphb_handle *h, const int *flags6_max);
 int sphb_slab_resort(sphb_handle *h);       /* after a poll saw 'order broken' on some rank */
 int sphb_slab_raise(sphb_handle *h);        /* the polled error code as status + message */
 int sphb_slab_step_end(sphb_handle *h);

@@ -165,7 +165,7 @@ def load_library():
     for name in ('step_begin', 'density', 'force_first', 'refine', 'step_end', 'init_lattice', 'prepass', 'records', 'forces', 'resort', 'raise'):
         getattr(L, 'sphb_slab_' + name).argtypes = [p]
     L.sphb_slab_poll.argtypes = [p, ip]
-    L.sphb_slab_check_halo.argtypes = [p, i]
+    L.sphb_slab_agree.argtypes = [p, ip]
     L.sphb_nccl_unique_id.argtypes = [p]
     L.sphb_slab_comm_init.argtypes = [p, p]
     L.sphb_slab_init_particles.argtypes = [p]

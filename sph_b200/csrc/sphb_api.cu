@@ -50,6 +50,8 @@ struct sphb_handle {
     int sw_G = 8, sw_L = 0, sw_B = 0, sw_nseg = 0;
     int sweep_blocks[2] = {0, 0};   // resident CTAs per SM of the G = 8 / G = 16 kernels (0 = not asked yet)
     long long sweep_steps = 0;
+    bool agreed_busy = true;      // x-slab runs: MAX over ranks of sweep_busy() for the step in flight
+    bool sweep_verify_pending = false;
     int sweep_flagged_last = 0, sweep_verify_fail_last = 0, sweep_burn_in_last = 0;
     double *gsum = nullptr;   // own-h gradient sums written by the density pass
     // ghost staging (2*pad each)
@@ -385,7 +387,6 @@ int sweep_occupancy(sphb_handle *H, bool adia, int *blocks) {
 int sweep_plan(sphb_handle *H) {
     H->sweep_used = false;
     if (H->opt.order != SPHB_ORDER_REFERENCE || !H->uniform_mass || H->opt.sweep_mode == SPHB_SWEEP_WORKLIST) return SPHB_OK;
-    if (H->slab) return SPHB_OK;
     if (H->opt.sweep_mode == SPHB_SWEEP_AUTO && !H->sweep_on) return SPHB_OK;
     if (H->na < 2) return SPHB_OK;
     const bool adia = H->cfg.pressure_calc == SPHB_ADIABATIC;
@@ -427,6 +428,7 @@ int launch_sweep(sphb_handle *H) {
         else k_force_sweep<false, 16><<<nblk(K.nseg, gpb), kSweepThreads, smem, H->stream>>>(K);
     }
     H->launches++;
+    H->sweep_verify_pending = true;
     CK(cudaGetLastError());
     return SPHB_OK;
 }
@@ -471,6 +473,9 @@ int step_begin(sphb_handle *H) {   // kick-drift + order flag, wall ghosts
     }
     phase_begin(H);
     TRY(launch_begin(H, 1));
+    // per-tile h maxima of a slab are gathered with atomicMax (its own tiles by the density pass, the halo's by the
+    // RECORDS unpack): start the step from zero
+    if (H->slab) CK(cudaMemsetAsync(H->thm, 0, sizeof(unsigned) * ((size_t)nblk(H->total, kTile) + 2), H->stream));
     TRY(launch_kick(H, 1));
     phase_end(H, 0);
     if (H->opt.sort_every_step) {
@@ -544,7 +549,7 @@ int step_force_first(sphb_handle *H) {
 
 int step_refine(sphb_handle *H, bool after_sweep = true) {   // runs until this handle's work list is empty
     if (H->opt.order == SPHB_ORDER_JACOBI) return SPHB_OK;
-    if (H->sweep_used && after_sweep) TRY(launch_sweep_verify(H));
+    if (H->sweep_verify_pending && after_sweep) { TRY(launch_sweep_verify(H)); H->sweep_verify_pending = false; }
     SweepArgs A = step_sweep_args(H);
     A.F.vA = H->vn; A.F.uA = H->un;   // lower-index neighbours are seen fully kicked
     TRY(launch_refine(H, A));
@@ -571,6 +576,14 @@ int step_error(sphb_handle *H) {    // turn the error word just read into a stat
     return code;
 }
 
+// Would work lists have (or did they have) much to do in the step just taken?  Every chunk with a non-zero kick
+// would have put at least one tile on a work list.
+bool sweep_busy(const sphb_handle *H) {
+    const int ntiles = nblk(H->na, kTile);
+    if (H->sweep_used) return H->h_ctl->sweep_moved_chunks >= ntiles / 16;
+    return H->sweep_on || H->h_ctl->tiles_swept > ntiles / 8 + 16;
+}
+
 int step_finish(sphb_handle *H) {
     H->epoch += H->opt.max_sweeps + 2;
     std::swap(H->v, H->vn);
@@ -588,9 +601,9 @@ int step_finish(sphb_handle *H) {
     H->sweeps_total += used;
     // Strategy of the next step (auto mode).  The serial sweep costs the same whatever the state; the work lists cost
     // next to nothing while almost no particle feels a non-zero kick (the undisturbed lattice with dyadic
-    // positions) and many times a sweep once every particle does.
+    // positions) and many times a sweep once every particle does.  The ranks of an x-slab run must all take the
+    // same strategy (it decides how many messages a step exchanges): they use the agreed flag.
     if (H->opt.order == SPHB_ORDER_REFERENCE) {
-        const int ntiles = nblk(H->na, kTile);
         if (H->sweep_used) {
             H->sweep_steps++;
             H->sweep_flagged_last = H->h_ctl->sweep_flagged;
@@ -599,11 +612,8 @@ int step_finish(sphb_handle *H) {
             // a burn-in that failed its check somewhere was too short for this state: lengthen it
             if (H->h_ctl->sweep_verify_fail > 0 && H->opt.sweep_burn_in <= 0)
                 H->sweep_burn_in_last = std::min(2 * H->sw_B, 512);
-            // every chunk with a non-zero kick would have put at least one tile on a work list
-            if (H->h_ctl->sweep_moved_chunks < ntiles / 16) H->sweep_on = false;
-        } else if (H->h_ctl->tiles_swept > ntiles / 8 + 16) {
-            H->sweep_on = true;
         }
+        H->sweep_on = H->slab ? H->agreed_busy : sweep_busy(H);
     }
     H->cfg.n_ghost = wall_ghosts(H);
     H->cfg.n_part = H->na + H->cfg.n_ghost;
@@ -700,6 +710,7 @@ SlabArgs slab_args(sphb_handle *H, int side) {
     SlabArgs A;
     A.x = H->x; A.m = H->m; A.vh = H->vh; A.uh = H->uh; A.vn = H->vn; A.un = H->un;
     A.h = H->h; A.rho = H->rho; A.P = H->P; A.idx = H->idx; A.rec = H->rec;
+    A.gsum = H->gsum; A.thm = H->thm;
     A.dirty = H->dirty; A.wl[0] = H->wl0; A.wl[1] = H->wl1; A.wl[2] = H->wl2; A.ctl = H->d_ctl;
     A.pad = H->pad; A.na = H->na; A.K = H->K; A.side = side;
     return A;
@@ -750,12 +761,16 @@ NcclApi g_nccl;
         }                                                                                 \
     } while (0)
 
-__global__ void k_flags(const Ctl *ctl, int *flags) {
+__global__ void k_flags(const Ctl *ctl, int *flags, int busy_if_not_swept, int ntiles, int swept) {
     flags[0] = ctl->err_code;
     flags[1] = ctl->unsorted;
     flags[2] = ctl->halo_changed;
     // the largest smoothing length this rank has seen, rounded up to float: positive floats order like ints
     flags[3] = __float_as_int(__double2float_ru(__longlong_as_double((long long)ctl->hmax_bits)));
+    // the thinner of my two halos, rounded down to float and turned round (MAX over ranks = thinnest halo of the run)
+    flags[4] = 0x7f800000 - __float_as_int(__double2float_rd(fmin(ctl->halo_thick[0], ctl->halo_thick[1])));
+    // sweep_busy() of this rank (the strategy of the next step follows the MAX over ranks)
+    flags[5] = swept ? (ctl->sweep_moved_chunks >= ntiles / 16) : (busy_if_not_swept || ctl->tiles_swept > ntiles / 8 + 16);
 }
 
 // pack both edges (one launch), one grouped send/recv with the neighbours, unpack both pads (one launch)
@@ -813,6 +828,22 @@ int native_attempt(sphb_handle *H, int *rounds) {
     H->part = 1; TRY(launch_density(H, 1, 0, 1, H->Pn));            // interior tiles
     H->part = 0;
     CK(cudaEventRecord(H->ev_base, H->stream));                     // interior density done
+    TRY(sweep_plan(H));
+    if (H->sweep_used) {
+        // The serial sweep walks the whole slab in one launch, the left halo included (it is the first segment's
+        // burn-in), so it starts when the RECORDS exchange has delivered the halo's records.  What it computed for
+        // the halo particles is compared with their owner's final values by the ONE ITERATE exchange that follows.
+        TRY(on_comm_stream(H, [&]() -> int { return native_exchange(H, MSG_RECORDS); }));
+        CK(cudaEventRecord(H->ev_rec, H->comm_stream));
+        CK(cudaStreamWaitEvent(H->stream, H->ev_rec, 0));
+        phase_end(H, 3);
+        TRY(launch_sweep(H));
+        phase_end(H, 4);
+        TRY(step_refine(H));
+        TRY(native_exchange(H, MSG_ITERATE));     // its unpack raises halo_changed if my estimate of a halo value was off
+        *rounds = 1;
+        return SPHB_OK;
+    }
     TRY(on_comm_stream(H, [&]() -> int {
         TRY(native_exchange(H, MSG_RECORDS));
         CK(cudaStreamWaitEvent(H->comm_stream, H->ev_base, 0));     // edge tiles read interior records next to them
@@ -838,30 +869,35 @@ int native_attempt(sphb_handle *H, int *rounds) {
     return SPHB_OK;
 }
 
-// The support of the largest smoothing length ANYWHERE in the run must fit inside this rank's halos: a wider one
-// could reach across a halo without either rank seeing the pair.  hmax_float_bits = MAX over ranks.
-int check_halo_width(sphb_handle *H, int hmax_float_bits) {
-    float hf;
+// The support of the largest smoothing length ANYWHERE in the run must fit inside EVERY rank's halos: a wider one
+// could reach across a halo without either rank seeing the pair.  Both numbers are agreed over all ranks (MAX of
+// flags[3], flags[4]), so every rank reaches the same verdict and leaves the step with the same status: a rank
+// returning alone would leave the others waiting in the next exchange for ever.
+int check_halo_width(sphb_handle *H, int hmax_float_bits, int thick_code) {
+    float hf, tf;
     memcpy(&hf, &hmax_float_bits, sizeof hf);
+    const int tb = 0x7f800000 - thick_code;
+    memcpy(&tf, &tb, sizeof tf);
     const double need = kRadius * (double)hf;
-    const double have = std::min(H->h_ctl->halo_thick[0], H->h_ctl->halo_thick[1]);
+    const double have = (double)tf;
     if (need > have) {
         char b[256];
-        snprintf(b, sizeof b, "x-slab halo (%.6g wide) thinner than the widest kernel support in the run (%.6g): raise halo_count", have, need);
+        snprintf(b, sizeof b, "thinnest x-slab halo of the run (%.6g wide) thinner than its widest kernel support (%.6g): raise halo_count", have, need);
         H->err = b;
         return SPHB_ERR_HALO;
     }
     return SPHB_OK;
 }
 
-int native_flags(sphb_handle *H) {   // -> H->h_flags[0..3] = MAX over ranks; H->h_ctl = my control block
-    k_flags<<<1, 1, 0, H->stream>>>(H->d_ctl, H->d_flags);
+int native_flags(sphb_handle *H) {   // -> H->h_flags[0..4] = MAX over ranks; H->h_ctl = my control block
+    k_flags<<<1, 1, 0, H->stream>>>(H->d_ctl, H->d_flags, H->sweep_on ? 1 : 0, nblk(H->na, kTile), H->sweep_used ? 1 : 0);
     H->launches++;
     CK(cudaGetLastError());
-    NK(g_nccl.AllReduce(H->d_flags, H->d_flags, 4, ncclInt32, ncclMax, H->comm, H->stream));
-    CK(cudaMemcpyAsync(H->h_flags, H->d_flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, H->stream));
+    NK(g_nccl.AllReduce(H->d_flags, H->d_flags, 6, ncclInt32, ncclMax, H->comm, H->stream));
+    CK(cudaMemcpyAsync(H->h_flags, H->d_flags, 6 * sizeof(int), cudaMemcpyDeviceToHost, H->stream));
     CK(cudaMemcpyAsync(H->h_ctl, H->d_ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, H->stream));
     CK(cudaStreamSynchronize(H->stream));
+    H->agreed_busy = H->h_flags[5] != 0;
     return SPHB_OK;
 }
 }  // namespace
@@ -1323,7 +1359,9 @@ int sphb_slab_refine(sphb_handle *H) {
 // The flags of the attempt in flight (the one host synchronisation of a slab step):
 //   flags[0] error code raised on the device (0 = none), flags[1] x-order broken by the drift,
 //   flags[2] the last ITERATE unpack differed from the copy held here (sweep not known finished),
-//   flags[3] the largest smoothing length seen here, as the bits of a float rounded up (orders like an int).
+//   flags[3] the largest smoothing length seen here, as the bits of a float rounded up (orders like an int),
+//   flags[4] the thinner of this rank's halos as 0x7f800000 - (bits of a float rounded down): MAX = thinnest,
+//   flags[5] work lists would have much to do on this rank (the sweep strategy of the next step follows the MAX).
 // Nothing is raised here: the ranks first agree (MAX over ranks) on what to do.
 int sphb_slab_poll(sphb_handle *H, int *flags) {
     if (!H || !flags) return SPHB_ERR_INVALID;
@@ -1334,12 +1372,21 @@ int sphb_slab_poll(sphb_handle *H, int *flags) {
     float up = (float)hm;
     if ((double)up < hm) up = __builtin_nextafterf(up, __builtin_inff());   // round up
     memcpy(&flags[3], &up, sizeof up);
+    const double th = std::min(H->h_ctl->halo_thick[0], H->h_ctl->halo_thick[1]);
+    float dn = (float)th;
+    if ((double)dn > th) dn = __builtin_nextafterf(dn, 0.0f);               // round down
+    int tb;
+    memcpy(&tb, &dn, sizeof tb);
+    flags[4] = 0x7f800000 - tb;
+    flags[5] = sweep_busy(H) ? 1 : 0;
     return SPHB_OK;
 }
-// after the ranks agreed on MAX(flags): does the widest kernel support of the run fit inside my halos?
-int sphb_slab_check_halo(sphb_handle *H, int hmax_float_bits) {
-    if (!H) return SPHB_ERR_INVALID;
-    return check_halo_width(H, hmax_float_bits);
+// After the ranks agreed on MAX(flags) of their polls: does the widest kernel support of the run fit inside its
+// thinnest halo (the same answer on every rank), and which sweep strategy does the next step take.
+int sphb_slab_agree(sphb_handle *H, const int *flags_max) {
+    if (!H || !flags_max) return SPHB_ERR_INVALID;
+    H->agreed_busy = flags_max[5] != 0;
+    return check_halo_width(H, flags_max[3], flags_max[4]);
 }
 // some rank's order flag was set: sort (if mine was), forget the attempt's errors, rebuild the ghosts
 int sphb_slab_resort(sphb_handle *H) {
@@ -1452,7 +1499,7 @@ int sphb_slab_step(sphb_handle *H, int nsteps) {
             H->err = "a neighbouring slab reported a device error";
             return H->h_flags[0];
         }
-        TRY(check_halo_width(H, H->h_flags[3]));
+        TRY(check_halo_width(H, H->h_flags[3], H->h_flags[4]));
         H->rounds_last = rounds;
         TRY(step_finish(H));
     }
@@ -1504,19 +1551,23 @@ int sphb_get_counters(sphb_handle *H, sphb_counters *out) {
     out->sweep_burn_in = H->sweep_used ? H->sw_B : 0;
     out->sweep_flagged = H->sweep_used ? H->h_ctl->sweep_flagged : 0;
     out->sweep_verify_fail = H->sweep_used ? H->h_ctl->sweep_verify_fail : 0;
-    if (H->have_counts) {
-        const int n = H->na;
-        std::vector<int> nw((size_t)n + 2 * H->pad), nb((size_t)n + 2 * H->pad);
-        TRY(sphb_download_counts(H, nw.data(), nb.data(), (int)nw.size()));
-        long long sum = 0;
-        int mn = 1 << 30, mx = 0;
-        for (int i = 0; i < n; i++) {
-            out->newton_hist[std::min(nw[(size_t)i], 11)]++;
-            sum += nb[(size_t)i];
-            mn = std::min(mn, nb[(size_t)i]);
-            mx = std::max(mx, nb[(size_t)i]);
-        }
-        out->nbr_min = mn; out->nbr_max = mx; out->nbr_mean = n ? (double)sum / n : 0.0;
+    if (H->have_counts && H->na > 0) {
+        // reduced on the device (the per-particle counts are 8 bytes each: half a gigabyte at 64 Mi particles);
+        // scratch: the gather temporary, free between steps
+        unsigned long long *d_out = reinterpret_cast<unsigned long long *>(H->tmp);
+        unsigned long long init[15] = {};
+        init[13] = ~0ull;
+        CK(cudaMemcpyAsync(d_out, init, sizeof init, cudaMemcpyHostToDevice, H->stream));
+        k_count_stats<<<std::max(1, std::min(nblk(H->na, 256), 4 * H->num_sms)), 256, 0, H->stream>>>(H->cnt, H->pad, H->na, d_out);
+        H->launches++;
+        CK(cudaGetLastError());
+        unsigned long long res[15];
+        CK(cudaMemcpyAsync(res, d_out, sizeof res, cudaMemcpyDeviceToHost, H->stream));
+        CK(cudaStreamSynchronize(H->stream));
+        for (int k = 0; k < 12; k++) out->newton_hist[k] = (long long)res[k];
+        out->nbr_mean = (double)res[12] / H->na;
+        out->nbr_min = (int)res[13];
+        out->nbr_max = (int)res[14];
     }
     return SPHB_OK;
 }

@@ -1029,6 +1029,8 @@ __global__ void __launch_bounds__(kSweepThreads, G == 8 ? 4 : 3) k_force_sweep(S
     }
     __syncwarp(gmask);
     int npairs_tot = 0, nmoved = 0, nflag = 0;
+    int tl_seen = -1;
+    double reach_loc = 0.0, x_far_l = -INFINITY, x_far_r = INFINITY;
 
 #pragma unroll 1
     for (int c = 0; c < nch; c++) {
@@ -1050,28 +1052,43 @@ __global__ void __launch_bounds__(kSweepThreads, G == 8 ? 4 : 3) k_force_sweep(S
         unsigned vmask = 0u, dmask = 0u;
         bool flag = false;
         if (eval) {
-            // the scan bound: 2.5 x the largest h of the three tiles around this particle, never above the global one
+            // the scan bound: 2.5 x the largest h of the three tiles around this particle, never above the global one;
+            // looked up again only when the particle enters another tile
             const int tl = s / kTile;
-            unsigned hb = K.thm[tl];
-            if (tl > 0) hb = max(hb, K.thm[tl - 1]);
-            if (tl + 1 < K.nthm) hb = max(hb, K.thm[tl + 1]);
-            const double reach_loc = fmin(reach_glob, kRadius * (double)__uint_as_float(hb));
-            // slot s + q, -G <= q < 2G, in the ring
-            auto rpos = [&](int q) { const int p = gl + q; return p < 0 ? bp * G + p + G : (p < G ? bc * G + p : bn * G + p - G); };
-            int dL = 0, dR = 0;                      // candidates per side; G = more than a group can hold
+            if (tl != tl_seen) {
+                tl_seen = tl;
+                unsigned hb = K.thm[tl];
+                if (tl > 0) hb = max(hb, K.thm[tl - 1]);
+                if (tl + 1 < K.nthm) hb = max(hb, K.thm[tl + 1]);
+                reach_loc = fmin(reach_glob, kRadius * (double)__uint_as_float(hb));
+                // tiles further away than the neighbouring ones are only covered by the global bound: the first slot
+                // of tile tl - 1 and the last of tile tl + 1 must be out of its reach
+                const int fl = (tl - 1) * kTile, fr = (tl + 2) * kTile - 1;
+                x_far_l = fl > lo ? __ldg(A.F.x + fl) : -INFINITY;
+                x_far_r = fr < hi - 1 ? __ldg(A.F.x + fr) : INFINITY;
+            }
+            // slot s + q, -G <= q < 2G, in the ring (the three chunks follow each other cyclically)
+            auto rpos = [&](int q) { int p = me + q; p -= p >= 3 * G ? 3 * G : 0; p += p < 0 ? 3 * G : 0; return p; };
+            int dL, dR;                              // candidates per side; G = more than a group can hold
+            if (G <= 8) {
+                // few slots: every one of them is a candidate (pair_geom drops those out of reach at once); only
+                // whether the first slot beyond the group's window could still interact has to be looked at
+                dL = (o.x - S.x[rpos(-G)]) < reach_loc ? G : R;
+                dR = (S.x[rpos(G)] - o.x) < reach_loc ? G : R;
+            } else {
+                dL = 0; dR = 0;
 #pragma unroll 1
-            while (dL < G && (o.x - S.x[rpos(-(dL + 1))]) < reach_loc) dL++;
+                while (dL < G && (o.x - S.x[rpos(-(dL + 1))]) < reach_loc) dL++;
 #pragma unroll 1
-            while (dR < G && (S.x[rpos(dR + 1)] - o.x) < reach_loc) dR++;
+                while (dR < G && (S.x[rpos(dR + 1)] - o.x) < reach_loc) dR++;
+            }
             if (store) {
                 if (dL == G || dR == G) flag = true;
-                // the scan stopped at the end of the array, not at a particle out of reach: next to a wall that is
+                // the array ends inside the window and its last particle is within reach: next to a wall that is
                 // the end of the world, on a slab edge the halo is thinner than the kernel reaches
-                if ((dL < G && s - (dL + 1) < lo && halo_l) || (dR < G && s + dR + 1 >= hi && halo_r)) raise(ctl, E_HALO, s);
-                // tiles further away than the neighbouring one are only covered by the global bound
-                const int fl = (tl - 1) * kTile, fr = (tl + 2) * kTile - 1;
-                if (fl > lo && (o.x - __ldg(A.F.x + fl)) < reach_glob) flag = true;
-                if (fr < hi - 1 && (__ldg(A.F.x + fr) - o.x) < reach_glob) flag = true;
+                if ((halo_l && s - G < lo && (o.x - S.x[rpos(lo - s)]) < reach_loc) ||
+                    (halo_r && s + G >= hi && (S.x[rpos(hi - 1 - s)] - o.x) < reach_loc)) raise(ctl, E_HALO, s);
+                if ((o.x - x_far_l) < reach_glob || (x_far_r - o.x) < reach_glob) flag = true;
             }
             dL = min(dL, R); dR = min(dR, R);
             npairs_tot++;                            // self: its energy term is evaluated by the reference too (and is exactly 0)
@@ -1079,7 +1096,7 @@ __global__ void __launch_bounds__(kSweepThreads, G == 8 ? 4 : 3) k_force_sweep(S
 #pragma unroll 1
             for (int d = dL; d >= 1; d--) {
                 const int p = gl - d;
-                const int rp = p < 0 ? bp * G + p + G : bc * G + p;
+                const int rp = rpos(-d);
                 const bool useA = S.idx[rp] < o.idx;             // the reference's sweep has already updated j
                 const double2 hc = useA ? S.hcA[rp] : S.hcB[rp], rk = useA ? S.rkA[rp] : S.rkB[rp];
                 Rec rj;
@@ -1105,8 +1122,7 @@ __global__ void __launch_bounds__(kSweepThreads, G == 8 ? 4 : 3) k_force_sweep(S
             // right-hand side, farthest first: old state
 #pragma unroll 1
             for (int d = dR; d >= 1; d--) {
-                const int p = gl + d;
-                const int rp = p < G ? bc * G + p : bn * G + p - G;
+                const int rp = rpos(d);
                 if (S.idx[rp] < o.idx) flag = true;              // overtaken: it is seen in its NEW state, which is not known yet
                 const double2 hc = S.hcB[rp], rk = S.rkB[rp];
                 Rec rj;
@@ -1125,9 +1141,8 @@ __global__ void __launch_bounds__(kSweepThreads, G == 8 ? 4 : 3) k_force_sweep(S
             S.vB[q] = nx.vB; S.uB[q] = nx.uB; S.vA[q] = nx.vB; S.uA[q] = nx.uB;
         }
         // the chain
-        double my_a = 0.0, my_e = 0.0, my_vf = vi, my_uf = ui;
 #pragma unroll
-        for (int t = 0; t < G; t++) {
+        for (int t = 0; t < G - 1; t++) {
             // merged exactly as the other force kernels merge them: (0 - left) + right, (0 + left) - right
             double a_s = (0.0 - aL) + aR, e_s = (0.0 + eL) - eR;
             a_s *= A.m0; e_s *= A.m0;
@@ -1135,7 +1150,6 @@ __global__ void __launch_bounds__(kSweepThreads, G == 8 ? 4 : 3) k_force_sweep(S
             // second half-kick, sph_simulation.cpp:105-106, operation by operation
             const double vf = __dadd_rn(vi, __dmul_rn(a_s, A.half_dt));
             const double uf = __dadd_rn(ui, __dmul_rn(e_s, A.half_dt));
-            if (gl == t) { my_a = a_s; my_e = e_s; my_vf = vf; my_uf = uf; }
             const double bv = __shfl_sync(gmask, vf, t, G), bu = __shfl_sync(gmask, uf, t, G);
             if (gl > t) {
                 const int q = t * R - (t * (t - 1)) / 2 + (gl - t - 1);
@@ -1148,6 +1162,12 @@ __global__ void __launch_bounds__(kSweepThreads, G == 8 ? 4 : 3) k_force_sweep(S
                 }
             }
         }
+        // every lane's left-hand sums are complete now (lane t's were when it was broadcast: same inputs, same bits)
+        double my_a = (0.0 - aL) + aR, my_e = (0.0 + eL) - eR;
+        my_a *= A.m0; my_e *= A.m0;
+        my_a = fma(-o.PrRho, gs_c, my_a);
+        const double my_vf = __dadd_rn(vi, __dmul_rn(my_a, A.half_dt));
+        const double my_uf = __dadd_rn(ui, __dmul_rn(my_e, A.half_dt));
         if (eval) { S.vA[me] = my_vf; S.uA[me] = my_uf; }
         bool moved = false;
         if (store) {
@@ -1455,16 +1475,18 @@ __global__ void k_pack_f64(const double *src, double *out, const unsigned *idx, 
 // neighbouring rank and fill ITS pad on the facing side, in the same ascending-x order, so that
 // every kernel above runs unchanged.  Messages are rows of K doubles plus a header row.
 //   BASE    after the drift:  x, m, v_half, u_half, h_old, rho_old, P, idx            (8 rows)
-//   RECORDS after the density pass: the owner's Rec2                                   (8 rows)
+//   RECORDS after the density pass: the owner's Rec2 and own-h gradient sum            (9 rows)
 //   ITERATE during the ordered sweep: current fully kicked v, u                        (2 rows)
 // header[0] = number of particles in the message.
 enum { MSG_BASE = 0, MSG_RECORDS = 1, MSG_ITERATE = 2 };
-__host__ __device__ inline int msg_rows(int what) { return what == MSG_ITERATE ? 2 : 8; }
+__host__ __device__ inline int msg_rows(int what) { return what == MSG_ITERATE ? 2 : (what == MSG_RECORDS ? 9 : 8); }
 
 struct SlabArgs {
     double *x, *m, *vh, *uh, *vn, *un, *h, *rho, *P;
     unsigned *idx;
     Rec2 *rec;
+    double *gsum;    // own-h gradient sums (the serial sweep evaluates the left halo's particles as its burn-in)
+    unsigned *thm;   // per-tile h maximum (see DensityArgs)
     int *dirty;
     int *wl[3];
     Ctl *ctl;
@@ -1486,6 +1508,7 @@ __device__ __forceinline__ void slab_pack_body(const SlabArgs &A, int what, doub
             const Rec2 r = A.rec[s];
             buf[0 * A.K + k] = r.A.h; buf[1 * A.K + k] = r.A.c5; buf[2 * A.K + k] = r.A.rho; buf[3 * A.K + k] = r.A.kap;
             buf[4 * A.K + k] = r.B.h; buf[5 * A.K + k] = r.B.c5; buf[6 * A.K + k] = r.B.rho; buf[7 * A.K + k] = r.B.kap;
+            buf[8 * A.K + k] = A.gsum[s];
         } else {
             buf[0 * A.K + k] = A.vn[s]; buf[1 * A.K + k] = A.un[s];
         }
@@ -1534,8 +1557,10 @@ __device__ __forceinline__ void slab_unpack_body(const SlabArgs &A, int what, co
             r.A.h = buf[0 * A.K + k]; r.A.c5 = buf[1 * A.K + k]; r.A.rho = buf[2 * A.K + k]; r.A.kap = buf[3 * A.K + k];
             r.B.h = buf[4 * A.K + k]; r.B.c5 = buf[5 * A.K + k]; r.B.rho = buf[6 * A.K + k]; r.B.kap = buf[7 * A.K + k];
             A.rec[s] = r;
-            // the scan bound of the force pass must cover the neighbour's smoothing lengths too
+            A.gsum[s] = buf[8 * A.K + k];
+            // the scan bounds of the force pass must cover the neighbour's smoothing lengths too
             atomicMax(&ctl->hmax_bits, (unsigned long long)__double_as_longlong(fmax(r.A.h, r.B.h)));
+            atomicMax(A.thm + s / kTile, __float_as_uint(__double2float_ru(fmax(r.A.h, r.B.h))));
         } else {
             const double v = buf[0 * A.K + k], u = buf[1 * A.K + k];
             if (__double_as_longlong(v) != __double_as_longlong(A.vn[s]) ||
@@ -1697,6 +1722,38 @@ __global__ void __launch_bounds__(256) k_diag_final(const double *partial, int n
         __syncthreads();
     }
     if (threadIdx.x < 4) out[threadIdx.x] = sh[threadIdx.x][0];
+}
+
+// ------------------------------------------------------------------------------------
+// Statistics of the most recent density pass over the alive particles, reduced on the device: Newton
+// iteration histogram (12 bins, the last one open), neighbour count minimum / maximum / sum.
+// out[0..11] histogram, out[12] sum, out[13] min, out[14] max (all unsigned long long, zeroed / preset by the caller).
+__global__ void __launch_bounds__(256) k_count_stats(const int *cnt, int pad, int na, unsigned long long *out) {
+    __shared__ unsigned hist[12];
+    __shared__ unsigned long long ssum;
+    __shared__ int smin, smax;
+    if (threadIdx.x < 12) hist[threadIdx.x] = 0u;
+    if (threadIdx.x == 0) { ssum = 0ull; smin = 0x7fffffff; smax = 0; }
+    __syncthreads();
+    unsigned long long sum = 0ull;
+    int mn = 0x7fffffff, mx = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < na; i += gridDim.x * blockDim.x) {
+        const int c = cnt[pad + i];
+        const int nb = c & 0xffffff;
+        atomicAdd(&hist[min((c >> 24) & 0xff, 11)], 1u);
+        sum += (unsigned long long)nb; mn = min(mn, nb); mx = max(mx, nb);
+    }
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_down_sync(0xffffffffu, sum, o);
+    mn = __reduce_min_sync(0xffffffffu, mn);
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    if ((threadIdx.x & 31) == 0) { atomicAdd(&ssum, sum); atomicMin(&smin, mn); atomicMax(&smax, mx); }
+    __syncthreads();
+    if (threadIdx.x < 12 && hist[threadIdx.x]) atomicAdd(out + threadIdx.x, (unsigned long long)hist[threadIdx.x]);
+    if (threadIdx.x == 0) {
+        atomicAdd(out + 12, ssum);
+        atomicMin(out + 13, (unsigned long long)smin);
+        atomicMax(out + 14, (unsigned long long)smax);
+    }
 }
 
 // ------------------------------------------------------------------------------------

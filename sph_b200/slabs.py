@@ -36,6 +36,7 @@ from typing import List
 from .api import Config, Simulation, SphbError
 
 MSG_BASE, MSG_RECORDS, MSG_ITERATE = 0, 1, 2
+NFLAGS = 6   # device error, order broken, halo changed, h max, thinnest halo, work lists busy (sphb_slab_poll)
 LEFT, RIGHT = -1, 1
 
 
@@ -98,9 +99,15 @@ class SlabRank(Simulation):
         self._check(getattr(self.L, "sphb_slab_" + name)(self.h, *args))
 
     def poll(self):
-        flags = (C.c_int * 4)()
+        flags = (C.c_int * NFLAGS)()
         self._check(self.L.sphb_slab_poll(self.h, flags))
-        return [flags[0], flags[1], flags[2], flags[3]]
+        return list(flags)
+
+    def agree(self, flags_max):
+        """The element-wise MAX over all ranks of the polled flags: halo-width verdict (the same on every rank) and
+        the sweep strategy of the next step."""
+        arr = (C.c_int * NFLAGS)(*[int(v) for v in flags_max])
+        self._check(self.L.sphb_slab_agree(self.h, arr))
 
 
 def _fields_by_index(ranks):
@@ -169,8 +176,8 @@ class DistTransport:
         import torch
         import torch.distributed as dist
         self.r, self.dist = rank_obj, dist
-        self.flag = torch.zeros(4, dtype=torch.int32, device=rank_obj.device)
-        self.host_flag = torch.zeros(4, dtype=torch.int32).pin_memory()
+        self.flag = torch.zeros(NFLAGS, dtype=torch.int32, device=rank_obj.device)
+        self.host_flag = torch.zeros(NFLAGS, dtype=torch.int32).pin_memory()
 
     def exchange(self, what):
         r = self.r
@@ -257,7 +264,7 @@ class SlabSimulation:
 
     def _flags(self):
         """MAX over all ranks of (device error, order broken, halo changed, largest h): the step's host sync."""
-        fl = [0, 0, 0, 0]
+        fl = [0] * NFLAGS
         for r in self.ranks:
             f = r.poll()
             fl = [max(a, b) for a, b in zip(fl, f)]
@@ -268,7 +275,8 @@ class SlabSimulation:
         for _ in range(nsteps):
             self._all("step_begin")
             rounds = self._attempt()
-            (err, unsorted, changed, hbits), mine = self._flags()
+            agreed, mine = self._flags()
+            err, unsorted, changed = agreed[:3]
             for _repair in range(2):
                 if not unsorted:
                     break
@@ -277,7 +285,8 @@ class SlabSimulation:
                 # (nothing of the previous state has been overwritten)
                 self._all("resort")
                 rounds = self._attempt()
-                (err, unsorted, changed, hbits), mine = self._flags()
+                agreed, mine = self._flags()
+                err, unsorted, changed = agreed[:3]
             if unsorted:
                 raise SphbError(11, "x-order still broken after the sort")
             while changed and not err:
@@ -286,13 +295,16 @@ class SlabSimulation:
                 self._all("refine")
                 self._exchange(MSG_ITERATE)
                 rounds += 1
-                (err, unsorted, changed, hbits), mine = self._flags()
+                agreed, mine = self._flags()
+                err, unsorted, changed = agreed[:3]
             if err:
                 for r in self.ranks:
                     r.call("raise")          # raises SphbError with the device's message on the rank that has it
                 raise SphbError(err, "a neighbouring slab reported device error %d" % err)
-            for r in self.ranks:     # the widest kernel support anywhere in the run must fit inside every halo
-                r._check(r.L.sphb_slab_check_halo(r.h, hbits))
+            # the widest kernel support anywhere in the run must fit inside its thinnest halo: judged from the agreed
+            # flags, so every rank raises (or not) together
+            for r in self.ranks:
+                r.agree(agreed)
             self.rounds_last = rounds
             self._all("step_end")
 

@@ -22,10 +22,11 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     n = int(os.environ.get("SLAB_CHECK_N", "200001"))
     cfg = Config(n_part=n, mass=4.0 / (n - 1), pressure_calc=1, t_i=0.005 * 100 / (n - 1))
-    one = Simulation(cfg, device=local)
+    mode = int(os.environ.get("SLAB_SWEEP", "0"))      # 0 auto, 1 work lists, 2 serial sweep
+    one = Simulation(cfg, device=local, sweep_mode=mode)
     one.init_lattice()
     native = os.environ.get("SLAB_NATIVE", "1") == "1"
-    sim = make_simulation(cfg, device=local, rank=rank, world=world, halo_count=128, native=native)
+    sim = make_simulation(cfg, device=local, rank=rank, world=world, halo_count=128, native=native, sweep_mode=mode)
     sim.init_lattice()
     bad = 0
     for st in range(0, 7):

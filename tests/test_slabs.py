@@ -95,16 +95,17 @@ def _cfg(n, pc):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("sweep_mode", [0, 1, 2])      # auto, work lists, serial sweep: the same bits
 @pytest.mark.parametrize("n,pc,varh,world", [(20001, 1, True, 2), (20001, 1, True, 3), (30000, 0, False, 2),
                                              (6001, 0, True, 4)])
-def test_slabs_in_one_process_match_single_handle_bit_for_bit(n, pc, varh, world):
+def test_slabs_in_one_process_match_single_handle_bit_for_bit(n, pc, varh, world, sweep_mode):
     from sph_b200 import Simulation
     from sph_b200.slabs import make_local_slabs
     cfg = _cfg(n, pc)
     fixed_h = 0.2 * 100 / (n - 1)
-    one = Simulation(cfg, variable_h=varh, fixed_h=fixed_h)
+    one = Simulation(cfg, variable_h=varh, fixed_h=fixed_h, sweep_mode=1)
     one.init_lattice()
-    many = make_local_slabs(cfg, world, variable_h=varh, fixed_h=fixed_h, halo_count=128)
+    many = make_local_slabs(cfg, world, variable_h=varh, fixed_h=fixed_h, halo_count=128, sweep_mode=sweep_mode)
     many.init_lattice()
     for st in range(0, 9):
         if st:
@@ -118,7 +119,42 @@ def test_slabs_in_one_process_match_single_handle_bit_for_bit(n, pc, varh, world
             assert np.array_equal(f1[:n], f2[:n]), "step %d: %s" % (st, np.argwhere(f1[:n] != f2[:n])[:4])
             assert np.array_equal(f1[n:, [0, 1, 2, 4, 6, 7]], f2[n:, [0, 1, 2, 4, 6, 7]])
     assert many.rounds_last >= 2
+    c = many.ranks[-1].counters()
+    if sweep_mode == 2:
+        # the serial sweep walked every slab, its left halo included, and what it computed for the halo particles
+        # was what their owner computed: no extra round was needed
+        assert c.sweep_steps == 8 and many.rounds_last == 2
+    if sweep_mode == 1:
+        assert c.sweep_steps == 0
     one.close()
+    many.close()
+
+
+@pytest.mark.gpu
+def test_too_thin_a_halo_is_reported_by_every_rank():
+    """The halo-width verdict is taken from flags agreed over all ranks: a rank raising alone would leave the
+    others waiting in the next exchange.  Here the ranks share a process; each is asked separately."""
+    from sph_b200 import SphbError
+    from sph_b200.slabs import make_local_slabs
+    cfg = _cfg(40001, 1)
+    many = make_local_slabs(cfg, 3, halo_count=12)       # enough for the kernel itself (~5 particles) ...
+    many.init_lattice()
+    many.step(2)
+    # ... but not for a smoothing length five times the lattice's, wherever in the run it sits
+    rec, ng = many.ranks[0].download()
+    rec = rec[:many.ranks[0].counters().n_alive].copy()
+    rec["h"][len(rec) // 2] *= 5.0
+    many.ranks[0].upload(rec, 0)
+    many._all("step_begin")
+    many._attempt()
+    agreed, _ = many._flags()
+    raised = 0
+    for r in many.ranks:
+        with pytest.raises(SphbError) as e:
+            r.agree(agreed)
+        assert e.value.code == 13
+        raised += 1
+    assert raised == 3
     many.close()
 
 
