@@ -143,6 +143,11 @@ int sphb_upload(sphb_handle *h, const sphb_particle *aos, int n_part, int n_ghos
  * reference side); 1 writes the ids seen by the last upload (faster, one contiguous copy). */
 int sphb_download(sphb_handle *h, sphb_particle *aos, int cap, int *n_part, int *n_ghost,
                   int write_ids);
+/* Snapshot for dumps (replaces the full copy behind SPHSimulation::file_write, sph_simulation.cpp:110-139, when only
+ * a sample of a large run is written): every `stride`-th alive record (array indices 0, stride, 2 stride, ...) followed
+ * by ALL ghost records; only those cross the PCIe link.  n_alive_out / n_ghost_out receive the counts written. */
+int sphb_download_strided(sphb_handle *h, sphb_particle *aos, int cap, int stride, int *n_alive_out,
+                          int *n_ghost_out, int write_ids);
 /* Same state as [n][9] doubles (mass,pos,vel,acc,h,du_dt,u,density,pressure) + type. */
 int sphb_download_fields(sphb_handle *h, double *fields, int *type, int cap, int *n_part,
                          int *n_ghost);

@@ -17,6 +17,7 @@ void setup_ghost_particles(ParticleArrayPtr &p_arr, Config &config) {
     Bridge &b = Bridge::get();
     sphb_handle *h = b.handle(alive_only);
     b.invalidate();   // the functor image no longer describes the device state
+    impose_fixed_h(reinterpret_cast<sphb_particle *>(p_arr.get()), n_alive);   // run-time fixed-h mode only
     int rc = sphb_upload(h, reinterpret_cast<const sphb_particle *>(p_arr.get()), n_alive, 0);
     int n_ghost = 0;
     if (!rc) rc = sphb_ghosts(h, &n_ghost);

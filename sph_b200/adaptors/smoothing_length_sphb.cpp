@@ -52,6 +52,7 @@ double calc_omega(const Particle &p, ParticleArrayPtr p_arr, Config c) {
     (void)p; (void)p_arr; (void)c;
     return 1;
 #else
+    if (sphb_adaptor::fixed_mode()) return 1;    // `variable_h 0` in the config file
     const long i = find(p, p_arr.get(), c.n_part);
     sphb_handle *h = nullptr;
     sphb_options o = sphb_adaptor::default_options();

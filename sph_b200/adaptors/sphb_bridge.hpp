@@ -16,7 +16,10 @@
 // adaptors exact for ANY call pattern, including the reference's in-place ordered sweep
 // (every kick invalidates the image: O(N) per call there, like the reference's own loops).
 #pragma once
+#include <cstdlib>
 #include <cstring>
+#include <fstream>
+#include <iostream>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -30,6 +33,76 @@ static_assert(sizeof(Config) == sizeof(sphb_config), "Config layout (basictypes.
 
 namespace sphb_adaptor {
 
+// Optional run-time keys, read from the SAME config file the reference's main.cpp reads (argv[1], else
+// ./config.txt: main.cpp:29-35), in the reference's own "KEY VALUE" / "#" comment syntax (setup.cpp:44-89).
+// The reference's ConfigReader only looks up the seven keys it knows (setup.cpp:27-33), so a config file carrying
+// these extra keys still works with the reference, and a shipped config without them works here:
+//   variable_h 0|1        per-particle root-find (1) or one fixed smoothing length (0); replaces the compile-time
+//                         switch USE_VARIABLE_H (define.hpp:27) — one binary serves both
+//   fixed_h <double>      that smoothing length (default CONSTANT_H, define.hpp:29)
+//   ordering reference|jacobi     sweep order of the second half of the step (sphb_options.order)
+//   sweep_rel_tol <double>        sphb_options.sweep_rel_tol
+//   sweep_mode auto|worklist|serial   sphb_options.sweep_mode
+//   dump_every <k>        file_write writes dumps/<step>.txt for every k-th step only (and the last one); the state is
+//                         copied back from the device only for those steps
+//   dump_stride <s>       ... and only every s-th alive particle of it (plus all ghosts)
+// SPHB_CONFIG in the environment names the file when the program's argv is not the reference's.
+struct RuntimeKeys {
+    int variable_h = -1;          // -1: not given
+    double fixed_h = -1.0;
+    int order = -1;
+    double sweep_rel_tol = -1.0;
+    int sweep_mode = -1;
+    int dump_every = 1, dump_stride = 1;
+};
+
+inline std::string config_path() {
+    if (const char *e = std::getenv("SPHB_CONFIG")) return e;
+    std::ifstream cmd("/proc/self/cmdline", std::ios::binary);   // argv, NUL-separated
+    std::string arg0, arg1;
+    if (cmd && std::getline(cmd, arg0, '\0') && std::getline(cmd, arg1, '\0') && !arg1.empty()) return arg1;
+    return "./config.txt";
+}
+
+inline int key_choice(const std::string &v, const char *const *names, int n, const char *key) {
+    for (int k = 0; k < n; k++)
+        if (v == names[k] || v == std::to_string(k)) return k;
+    std::cerr << "[ERROR] Failed to parse value '" << v << "' for property '" << key << "'." << std::endl;
+    std::exit(1);   // what the reference's reader does with a value it cannot parse (setup.cpp:104-135)
+}
+
+inline const RuntimeKeys &runtime_keys() {
+    static RuntimeKeys keys;
+    static bool loaded = false;
+    if (loaded) return keys;
+    loaded = true;
+    std::ifstream in(config_path());
+    std::string l;
+    while (in && std::getline(in, l)) {
+        if (l.empty() || l[0] == '#') continue;
+        const size_t space = l.find(' ');
+        if (space == std::string::npos || space == 0 || space + 1 >= l.size()) continue;   // the reference's reader reports these
+        const std::string name = l.substr(0, space);
+        std::string value = l.substr(space + 1);
+        while (!value.empty() && (value.back() == ' ' || value.back() == '\r' || value.back() == '\t')) value.pop_back();
+        try {
+            static const char *const orders[] = {"reference", "jacobi"};
+            static const char *const modes[] = {"auto", "worklist", "serial"};
+            if (name == "variable_h") keys.variable_h = std::stoi(value) != 0;
+            else if (name == "fixed_h") keys.fixed_h = std::stod(value);
+            else if (name == "ordering") keys.order = key_choice(value, orders, 2, "ordering");
+            else if (name == "sweep_rel_tol") keys.sweep_rel_tol = std::stod(value);
+            else if (name == "sweep_mode") keys.sweep_mode = key_choice(value, modes, 3, "sweep_mode");
+            else if (name == "dump_every") keys.dump_every = std::max(1, std::stoi(value));
+            else if (name == "dump_stride") keys.dump_stride = std::max(1, std::stoi(value));
+        } catch (const std::exception &) {
+            std::cerr << "[ERROR] Failed to parse value '" << value << "' for property '" << name << "'." << std::endl;
+            std::exit(1);
+        }
+    }
+    return keys;
+}
+
 inline sphb_options default_options() {
     sphb_options o;
     sphb_default_options(&o);
@@ -39,7 +112,23 @@ inline sphb_options default_options() {
     o.variable_h = 0;
 #endif
     o.fixed_h = CONSTANT_H; // define.hpp:29
+    const RuntimeKeys &k = runtime_keys();
+    if (k.variable_h >= 0) o.variable_h = k.variable_h;
+    if (k.fixed_h > 0) o.fixed_h = k.fixed_h;
+    if (k.order >= 0) o.order = k.order;
+    if (k.sweep_rel_tol >= 0) o.sweep_rel_tol = k.sweep_rel_tol;
+    if (k.sweep_mode >= 0) o.sweep_mode = k.sweep_mode;
     return o;
+}
+
+// One fixed smoothing length for every particle?  (The reference's fixed-h build gives every particle CONSTANT_H in
+// init_particles, setup.cpp:181-184.  With the run-time key the reference's unchanged init_particles has stored
+// h_factor * spacing instead, so the adaptors put the fixed value in whenever they take the array to the device.)
+inline bool fixed_mode() { return default_options().variable_h == 0; }
+inline void impose_fixed_h(sphb_particle *rec, int n) {
+    if (!fixed_mode()) return;
+    const double h = default_options().fixed_h;
+    for (int k = 0; k < n; k++) rec[k].h = h;
 }
 
 [[noreturn]] inline void fail(sphb_handle *h, int rc) {
@@ -121,13 +210,13 @@ private:
     bool same_density_inputs(const Particle *arr, int i) const {
         for (int k = 0; k < n_; k++)
             if (arr[k].pos != image_[(size_t)k].pos || arr[k].mass != image_[(size_t)k].mass) return false;
-        return arr[i].h == image_[(size_t)i].h;
+        return fixed_mode() || arr[i].h == image_[(size_t)i].h;
     }
     bool same_force_inputs(const Particle *arr, int i, bool own_pressure) const {
         for (int k = 0; k < n_; k++) {
             const sphb_particle &s = image_[(size_t)k];
             const Particle &a = arr[k];
-            if (a.pos != s.pos || a.vel != s.vel || a.h != s.h || a.u != s.u || a.density != s.density ||
+            if (a.pos != s.pos || a.vel != s.vel || (a.h != s.h && !fixed_mode()) || a.u != s.u || a.density != s.density ||
                 a.mass != s.mass || (int)a.type != s.type)
                 return false;
         }
@@ -139,6 +228,7 @@ private:
         g_ = c.n_ghost;
         image_.resize((size_t)n_);
         std::memcpy(image_.data(), arr, sizeof(sphb_particle) * (size_t)n_);
+        impose_fixed_h(image_.data(), n_);
         int rc = sphb_upload(h_, image_.data(), n_, g_);
         if (rc) { image_valid_ = false; fail(h_, rc); }
         image_valid_ = true;

@@ -143,6 +143,7 @@ def load_library():
     L.sphb_set_stream.argtypes = [p, p]
     L.sphb_upload.argtypes = [p, p, i, i]
     L.sphb_download.argtypes = [p, p, i, ip, ip, i]
+    L.sphb_download_strided.argtypes = [p, p, i, i, ip, ip, i]
     L.sphb_download_fields.argtypes = [p, p, p, i, ip, ip]
     L.sphb_download_counts.argtypes = [p, p, p, i]
     L.sphb_init_lattice.argtypes = [p]
@@ -265,6 +266,15 @@ class Simulation:
         self._check(self.L.sphb_download(self.h, out.ctypes.data, len(out), C.byref(n), C.byref(g),
                                          int(write_ids)))
         return out[: n.value], g.value
+
+    def download_strided(self, stride, out: np.ndarray = None, write_ids=True):
+        """Every stride-th alive record followed by all ghost records: (records, n_alive_written, n_ghost)."""
+        if out is None:
+            out = np.zeros(self._cap // stride + 2 + 2 * 4096, dtype=PARTICLE_DTYPE)
+        na, g = C.c_int(), C.c_int()
+        self._check(self.L.sphb_download_strided(self.h, out.ctypes.data, len(out), int(stride), C.byref(na),
+                                                 C.byref(g), int(write_ids)))
+        return out[: na.value + g.value], na.value, g.value
 
     def fields(self):
         """([n, 9] doubles, type[n], n_ghost) in array-index order."""

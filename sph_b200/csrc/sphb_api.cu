@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstddef>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -136,6 +137,26 @@ const char *err_text(int code) {
     }
 }
 
+constexpr size_t kErrBytes = 2 * sizeof(int) + sizeof(unsigned long long);   // err_code, err_unused, err_first
+static_assert(offsetof(Ctl, err_first) == offsetof(Ctl, err_code) + 2 * sizeof(int), "the error words are cleared with one memset");
+
+// The device error word -> status + message.  Reported is the LOWEST sorted slot that raised and ITS code: with the
+// array order equal to the x order that is the particle the reference's sequential loops fail at first.
+int decode_error(const Ctl &c, const unsigned *d_idx, char *msg, size_t cap) {
+    const unsigned long long packed = ~c.err_first;
+    const int code = (int)(packed & 0xff);
+    const int slot = (int)(packed >> 8) - 1;
+    if (slot < 0) { snprintf(msg, cap, "%s", err_text(code)); return code; }
+    unsigned pidx = 0;
+    if (d_idx && cudaMemcpy(&pidx, d_idx + slot, sizeof pidx, cudaMemcpyDeviceToHost) == cudaSuccess) {
+        if (pidx & kGhostBit) snprintf(msg, cap, "%s (ghost of particle %u, sorted slot %d)", err_text(code), pidx & ~kGhostBit, slot);
+        else snprintf(msg, cap, "%s (particle %u, sorted slot %d)", err_text(code), pidx, slot);
+    } else {
+        snprintf(msg, cap, "%s (particle %d)", err_text(code), slot);
+    }
+    return code;
+}
+
 template <class T>
 int dalloc(sphb_handle *H, T **p, size_t n) {
     CK(cudaMalloc((void **)p, sizeof(T) * std::max<size_t>(n, 1)));
@@ -150,11 +171,10 @@ int read_ctl(sphb_handle *H) {
     CK(cudaStreamSynchronize(H->stream));
     if (H->h_ctl->err_code != 0) {
         char b[256];
-        snprintf(b, sizeof b, "%s (sorted slot %d)", err_text(H->h_ctl->err_code), H->h_ctl->err_particle);
+        const int code = decode_error(*H->h_ctl, H->idx, b, sizeof b);
         H->err = b;
-        int code = H->h_ctl->err_code;
         // clear so that the handle stays usable after the caller has seen the error
-        CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, 2 * sizeof(int), H->stream));
+        CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, kErrBytes, H->stream));
         return code;
     }
     return SPHB_OK;
@@ -401,7 +421,10 @@ int sweep_plan(sphb_handle *H) {
         const long long lmax = 2048;
         const long long waves = std::max(1ll, (H->na + resident * lmax - 1) / (resident * lmax));
         L = (int)((H->na + resident * waves - 1) / (resident * waves));
-        L = std::max(L, 4 * B);                          // burn-in at most a quarter of the work
+        // several waves: keep the burn-in below a quarter of the work.  A single wave that does not even fill the
+        // machine is latency-bound (a group's time is proportional to L + B): shorter segments, down to the burn-in
+        // length, finish sooner although they do more work in total.
+        L = std::max(L, waves > 1 ? 4 * B : B);
     }
     L = std::max(B, (L + G - 1) / G * G);
     H->sw_G = G; H->sw_L = L; H->sw_B = B; H->sw_nseg = nblk(H->na, L);
@@ -569,10 +592,9 @@ int step_flags(sphb_handle *H, int *err, int *unsorted, int *halo_changed) {
 
 int step_error(sphb_handle *H) {    // turn the error word just read into a status
     char b[256];
-    snprintf(b, sizeof b, "%s (sorted slot %d)", err_text(H->h_ctl->err_code), H->h_ctl->err_particle);
+    const int code = decode_error(*H->h_ctl, H->idx, b, sizeof b);
     H->err = b;
-    const int code = H->h_ctl->err_code;
-    CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, 2 * sizeof(int), H->stream));
+    CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, kErrBytes, H->stream));
     return code;
 }
 
@@ -631,7 +653,7 @@ int step_once(sphb_handle *H) {
         TRY(step_flags(H, &err, &unsorted, &changed));
         if (unsorted && attempt < 2) {
             // whatever the kernels complained about came from the broken order: forget it, repair, redo
-            CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, 2 * sizeof(int), H->stream));
+            CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, kErrBytes, H->stream));
             TRY(step_resort(H));
             continue;
         }
@@ -1098,6 +1120,28 @@ int sphb_download(sphb_handle *H, sphb_particle *aos, int cap, int *n_part, int 
     return SPHB_OK;
 }
 
+int sphb_download_strided(sphb_handle *H, sphb_particle *aos, int cap, int stride, int *n_alive_out, int *n_ghost_out,
+                          int write_ids) {
+    if (!H || !aos || stride < 1) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    int n = 0;
+    TRY(pack_to_staging(H, false, &n));              // records in array-index order in the device staging buffer
+    const int ng = n - H->na;
+    const int na_out = (H->na + stride - 1) / stride;
+    if (na_out + ng > cap) { H->err = "download buffer too small"; return SPHB_ERR_CAPACITY; }
+    const size_t skip = write_ids ? 0 : 8;           // write_ids = 0: the 8 leading bytes (const int id + padding) stay
+    if (na_out > 0)
+        CK(cudaMemcpy2DAsync((char *)aos + skip, sizeof(AosRec), (const char *)H->d_aos + skip, sizeof(AosRec) * (size_t)stride,
+                             sizeof(AosRec) - skip, (size_t)na_out, cudaMemcpyDeviceToHost, H->stream));
+    if (ng > 0)
+        CK(cudaMemcpy2DAsync((char *)(aos + na_out) + skip, sizeof(AosRec), (const char *)(H->d_aos + H->na) + skip, sizeof(AosRec),
+                             sizeof(AosRec) - skip, (size_t)ng, cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaStreamSynchronize(H->stream));
+    if (n_alive_out) *n_alive_out = na_out;
+    if (n_ghost_out) *n_ghost_out = ng;
+    return SPHB_OK;
+}
+
 int sphb_download_fields(sphb_handle *H, double *fields, int *type, int cap, int *n_part, int *n_ghost) {
     if (!H || !fields) return SPHB_ERR_INVALID;
     CK(cudaSetDevice(H->device));
@@ -1392,7 +1436,7 @@ int sphb_slab_agree(sphb_handle *H, const int *flags_max) {
 int sphb_slab_resort(sphb_handle *H) {
     if (!H) return SPHB_ERR_INVALID;
     CK(cudaSetDevice(H->device));
-    CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, 2 * sizeof(int), H->stream));
+    CK(cudaMemsetAsync(&H->d_ctl->err_code, 0, kErrBytes, H->stream));
     if (H->h_ctl->unsorted) return step_resort(H);
     TRY(launch_begin(H, 1));
     TRY(launch_kick(H, 0));
@@ -1675,9 +1719,9 @@ int sphb_density_static(const double *d_x, const double *d_h, const double *d_rh
     CK(cudaStreamSynchronize(st));
     if (host_ctl.err_code != 0) {
         char b[256];
-        snprintf(b, sizeof b, "%s (particle %d)", err_text(host_ctl.err_code), host_ctl.err_particle);
+        const int code = decode_error(host_ctl, nullptr, b, sizeof b);   // no index array here: slot = particle
         H->err = b;
-        return host_ctl.err_code;
+        return code;
     }
     return SPHB_OK;
 }

@@ -49,7 +49,9 @@ struct Ctl {
     int GL, GR;                    // ghosts currently in the left / right pad
     int ncand;                     // ghost candidates appended this step
     int unsorted;                  // order check failed
-    int err_code, err_particle;    // first error wins
+    int err_code, err_unused;      // some error was raised (whichever thread came first)
+    unsigned long long err_first;  // ~(((slot + 1) << 8) | code) of the LOWEST slot that raised (atomicMax; 0 = none): the
+                                   // particle the reference's sequential loops would have failed at
     unsigned long long hmax_bits;  // max over every h (old and new) in [lo,hi), as ordered bits
     unsigned long long fallbacks;  // bisection fallbacks taken
     int nwork[3];                  // tiles in the work list of the sweep whose stamp is k mod 3
@@ -74,7 +76,8 @@ struct Ctl {
 };
 
 __device__ __forceinline__ void raise(Ctl *ctl, int code, int particle) {
-    if (atomicCAS(&ctl->err_code, 0, code) == 0) ctl->err_particle = particle;
+    atomicCAS(&ctl->err_code, 0, code);
+    atomicMax(&ctl->err_first, ~((((unsigned long long)(unsigned)(particle + 1)) << 8) | (unsigned long long)code));
 }
 
 // ------------------------------------------------------------------------------------
@@ -296,6 +299,7 @@ __global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs
         double hnew = hold, rhonew = rhoold, om_new = 1.0, om_stale = 1.0;
         int iters = 0, cnt = 0;
         bool tiny = false;
+        bool failed = false;     // the root-find of this particle raised: the reference never reaches its density guard
         (void)tiny;
         double Sw, Sg, Sgr = 0.0;
         // 1/h, h and sum_j m_j dW/dh of the first and of the most recent evaluation: the records below are built
@@ -326,7 +330,7 @@ __global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs
 #pragma unroll 1
                 while (cont && iters < kMaxIterNR) {
                     iters++;
-                    if (df == 0.0) { raise(ctl, E_ZERO_DERIVATIVE, s); break; }
+                    if (df == 0.0) { raise(ctl, E_ZERO_DERIVATIVE, s); failed = true; break; }
                     const double xn = xcur - f / df;
                     if (fabs(xn - xcur) <= kTinyStep * fabs(xn)) {
                         // The step did not move h beyond 1e-12 relative: this iteration passes the stop test
@@ -341,12 +345,16 @@ __global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs
                         break;
                     }
                     SPHB_EVAL(xn, f, df, dsum);
-                    if (!isfinite(f) || !isfinite(df)) { raise(ctl, E_NOT_FINITE, s); break; }
+                    if (!isfinite(f) || !isfinite(df)) { raise(ctl, E_NOT_FINITE, s); failed = true; break; }
                     const double xprev = xcur;
                     xcur = xn;
                     cont = !(fabs(xcur - xprev) < kHEps * fabs(xcur) || xcur == xprev);
                 }
-                if (cont && ctl->err_code == 0) {
+                // (the fallback is a thousand window scans: once an error has been raised at a LOWER slot this particle's
+                // cannot become the one reported, and it is skipped; a higher slot's error must not stop it — the first
+                // failing particle is reported, whichever thread got there first)
+                if (cont && (*((volatile unsigned long long *)&ctl->err_first) == 0ull ||
+                             ((~*((volatile unsigned long long *)&ctl->err_first)) >> 8) > (unsigned long long)(s + 1))) {
                     // bisection fallback on [1e-8, 2 limit], gsl_root_test_interval rel 1e-4
                     // (its bracket end 2*limit sums over the whole domain: a slab cannot evaluate it)
                     if (ctl->halo_left | ctl->halo_right) raise(ctl, E_HALO, s);
@@ -356,8 +364,8 @@ __global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs
                     SPHB_EVAL(xl, fl, dfx, dsx);
                     SPHB_EVAL(xh, fh, dfx, dsx);
                     double root = 0.5 * (xl + xh);
-                    if (!isfinite(fl) || !isfinite(fh)) raise(ctl, E_NOT_FINITE, s);
-                    else if ((fl < 0.0 && fh < 0.0) || (fl > 0.0 && fh > 0.0)) raise(ctl, E_NO_BRACKET, s);
+                    if (!isfinite(fl) || !isfinite(fh)) { raise(ctl, E_NOT_FINITE, s); failed = true; }
+                    else if ((fl < 0.0 && fh < 0.0) || (fl > 0.0 && fh > 0.0)) { raise(ctl, E_NO_BRACKET, s); failed = true; }
                     else {
                         int it = 0;
                         bool go = true;
@@ -370,7 +378,7 @@ __global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs
                                 const double mid = (xl + xh) / 2.0;
                                 double fm;
                                 SPHB_EVAL(mid, fm, dfx, dsx);
-                                if (!isfinite(fm)) { raise(ctl, E_NOT_FINITE, s); break; }
+                                if (!isfinite(fm)) { raise(ctl, E_NOT_FINITE, s); failed = true; break; }
                                 if (fm == 0.0) { root = mid; xl = mid; xh = mid; }
                                 else if ((fl > 0.0 && fm < 0.0) || (fl < 0.0 && fm > 0.0)) {
                                     root = 0.5 * (xl + mid); xh = mid; fh = fm;
@@ -387,7 +395,7 @@ __global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs
                     xcur = root;
                     SPHB_EVAL(xcur, f, df, dsum);
                 }
-                if (xcur < 0) raise(ctl, E_NEGATIVE_H, s);
+                if (xcur < 0) { raise(ctl, E_NEGATIVE_H, s); failed = true; }
                 hnew = xcur;
                 rhonew = rho_cur;
                 if (A.omn) om_new = 1.0 - dsum * (-hnew / rhonew);
@@ -431,7 +439,7 @@ __global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs
         if (is_pad && A.Pn != A.P) A.Pn[s] = A.P[s];
         // ensure_nonzero_density (calculators.cpp:174-186) guards every particle a force sum
         // touches, in whichever state (new, or old when check_old) it will be seen
-        if (rhonew < kEps || (A.check_old && rhoold < kEps)) raise(ctl, E_LOW_DENSITY, s);
+        if (!failed && (rhonew < kEps || (A.check_old && rhoold < kEps))) raise(ctl, E_LOW_DENSITY, s);
         hloc = fmax(hnew, hold);
     }
     // window scans of this tile (one atomic per warp)

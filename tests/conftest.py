@@ -58,23 +58,39 @@ def cuda_available():
         return False
 
 
-def assert_neighbour_counts(nb_gpu, nb_ref, ref_fields, n_alive, what, delta=1e-10):
-    """Neighbour counts (#{k : |x_i - x_k| / h_i < 2.5}, self and ghosts included) must be EQUAL,
-    except where the reference's own state puts a neighbour within the h-parity tolerance
-    (relative `delta`) of the support edge.  That case is systematic, not rare: in the undisturbed
-    lattice h = h_factor * spacing = 2 * spacing is an exact root, so the fifth neighbour sits
-    at q = 2.5 to the last bit and rounding noise in h (summation order, pow() vs products)
-    decides the comparison.  For those particles both counts must lie in the
-    bracket [#{q < 2.5(1-delta)}, #{q < 2.5(1+delta)}] computed from the reference state.
-    Returns the number of bracketed (straddling) mismatches."""
+def assert_neighbour_counts(nb_gpu, nb_ref, ref_fields, n_alive, what, delta=1e-10, allow_edge=True):
+    """Neighbour counts (#{k : |x_i - x_k| / h_i < 2.5}, self and ghosts included) must be EQUAL.
+
+    One exception can be allowed (allow_edge): a particle whose reference state puts a neighbour within the
+    h-parity tolerance (relative `delta`) of the support edge.  That case is systematic in the undisturbed
+    lattice, where h = h_factor * spacing = 2 * spacing is an exact root, the fifth neighbour sits at q = 2.5 to
+    the last bit, and rounding noise in h (summation order, pow() vs products) decides the comparison (SURVEY.md
+    §7.3-3).  For such a particle both counts must lie in the bracket [#{q < 2.5(1-delta)}, #{q < 2.5(1+delta)}]
+    computed from the reference state.  Every mismatch is counted and its margin |q - 2.5| / 2.5 measured; the
+    numbers are printed (pytest -s / the captured log) and returned as a dict, so that callers on states without
+    that degeneracy can — and do — demand zero mismatches (allow_edge=False)."""
     nb_gpu = np.asarray(nb_gpu[:n_alive], dtype=np.int64)
     nb_ref = np.asarray(nb_ref[:n_alive], dtype=np.int64)
     bad = np.nonzero(nb_gpu != nb_ref)[0]
+    stats = dict(what=what, particles=int(n_alive), mismatches=int(bad.size), largest_margin=0.0, smallest_margin=None)
     if bad.size == 0:
-        return 0
+        print("neighbour counts %s: %d particles, 0 mismatches" % (what, n_alive))
+        return stats
     x_all = np.sort(ref_fields[:, 1])
     xi = ref_fields[bad, 1]
     r = 2.5 * ref_fields[bad, 4]
+    # margin of the neighbour that decides the difference: the one closest to the support edge, on either side
+    margins = np.full(bad.size, np.inf)
+    for edge in (xi - r, xi + r):                                # the particles next to either end of the support
+        k = np.searchsorted(x_all, edge)
+        for kk in (np.clip(k - 1, 0, x_all.size - 1), np.clip(k, 0, x_all.size - 1)):
+            margins = np.minimum(margins, np.abs(np.abs(x_all[kk] - xi) / r - 1.0))
+    stats["largest_margin"] = float(margins.max())
+    stats["smallest_margin"] = float(margins.min())
+    print("neighbour counts %s: %d particles, %d mismatches, margins |q/2.5 - 1| between %.2e and %.2e" % (
+        what, n_alive, bad.size, margins.min(), margins.max()))
+    assert allow_edge, "%s: %d neighbour counts differ (first: particle %d, %d vs %d, margin %.2e)" % (
+        what, bad.size, int(bad[0]), int(nb_gpu[bad[0]]), int(nb_ref[bad[0]]), margins[0])
     lo_in = np.searchsorted(x_all, xi - r * (1 - delta), side="right")
     hi_in = np.searchsorted(x_all, xi + r * (1 - delta), side="left")
     lo_out = np.searchsorted(x_all, xi - r * (1 + delta), side="right")
@@ -83,4 +99,15 @@ def assert_neighbour_counts(nb_gpu, nb_ref, ref_fields, n_alive, what, delta=1e-
     ok = (c_min <= nb_gpu[bad]) & (nb_gpu[bad] <= c_max) & (c_min <= nb_ref[bad]) & (nb_ref[bad] <= c_max)
     assert ok.all(), "%s: %d neighbour counts differ away from the support edge (first: particle %d, %d vs %d)" % (
         what, int((~ok).sum()), int(bad[~ok][0]), int(nb_gpu[bad[~ok][0]]), int(nb_ref[bad[~ok][0]]))
-    return int(bad.size)
+    assert margins.max() <= delta * 1.01, "%s: a mismatching particle is %.2e away from the support edge" % (what, margins.max())
+    return stats
+
+
+def reference_neighbour_counts(fields):
+    """#{k : |x_i - x_k| / h_i < 2.5} for every particle of a golden state, with the reference's own expression
+    (kernel.cpp:31 decides `q < 5./2.` on q = std::abs(p.pos - p_j.pos) / h, smoothing_length.cpp:84): IEEE
+    subtraction, absolute value, division and comparison, which numpy float64 reproduces bit for bit."""
+    x = fields[:, 1]
+    h = fields[:, 4]
+    q = np.abs(x[:, None] - x[None, :]) / h[:, None]
+    return (q < 2.5).sum(axis=1).astype(np.int32)

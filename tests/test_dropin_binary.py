@@ -27,10 +27,10 @@ t_i 0.005
 """
 
 
-def _run(binary, workdir, pc):
+def _run(binary, workdir, pc, extra=""):
     os.makedirs(workdir, exist_ok=True)
     with open(os.path.join(workdir, "config.txt"), "w") as f:
-        f.write(CONFIG.format(pc=pc))
+        f.write(CONFIG.format(pc=pc) + extra)
     res = subprocess.run([binary, "config.txt"], cwd=workdir, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
                          text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-2000:]
@@ -49,14 +49,22 @@ def _load(path):
     return ids, types, np.array(rows)
 
 
-@pytest.mark.parametrize("binary,ref,pc", [("sph_dropin", "sph_ref", 1), ("sph_dropin", "sph_ref", 0)])
-def test_dropin_program_reproduces_the_reference_dumps(tmp_path, binary, ref, pc):
+# Optional keys the adaptors read from the same config file (sph_b200/adaptors/sphb_bridge.hpp).  The reference's reader
+# looks up only its own seven keys (setup.cpp:27-33), so BOTH programs are given the extended file: `variable_h 0` makes
+# the one drop-in binary behave like the reference's fixed-h BUILD (its compile-time switch, define.hpp:27-29).
+FIXED = "variable_h 0\nfixed_h 0.2\n# sweep strategy: same results either way\nsweep_mode serial\n"
+
+
+@pytest.mark.parametrize("binary,ref,pc,extra", [("sph_dropin", "sph_ref", 1, ""), ("sph_dropin", "sph_ref", 0, ""),
+                                                 ("sph_dropin", "sph_ref_fixedh", 1, FIXED),
+                                                 ("sph_dropin", "sph_ref_fixedh", 0, FIXED)])
+def test_dropin_program_reproduces_the_reference_dumps(tmp_path, binary, ref, pc, extra):
     exe = os.path.join(DROPIN, binary)
     ref_exe = os.path.join(ROOT, "oracle", "_ref", ref)
     if not (os.path.exists(exe) and os.path.exists(ref_exe)):
         pytest.skip("drop-in / reference binaries not built (need the reference sources)")
-    _run(exe, str(tmp_path / "ours"), pc)
-    _run(ref_exe, str(tmp_path / "ref"), pc)
+    _run(exe, str(tmp_path / "ours"), pc, extra)
+    _run(ref_exe, str(tmp_path / "ref"), pc, extra)
     ours = sorted(os.listdir(tmp_path / "ours" / "dumps"), key=lambda s: int(s[:-4]))
     theirs = sorted(os.listdir(tmp_path / "ref" / "dumps"), key=lambda s: int(s[:-4]))
     assert ours == theirs and len(ours) == 201
@@ -77,3 +85,31 @@ def test_dropin_program_reproduces_the_reference_dumps(tmp_path, binary, ref, pc
         assert (d <= lim).all(), "%s: %s" % (name, np.argwhere(d > lim)[:5])
         worst = max(worst, float(d.max()))
     print("worst printed difference over 201 dumps: %.2e" % worst)
+
+
+def test_dropin_program_thinned_out_dumps(tmp_path):
+    """`dump_every 50` + `dump_stride 10`: only steps 0, 50, ..., 200 are dumped (the state stays on the device in
+    between), each with every 10th alive particle and all ghosts — the same rows as in the reference's full dumps."""
+    exe = os.path.join(DROPIN, "sph_dropin")
+    if not (os.path.exists(exe) and os.path.exists(REF_BIN)):
+        pytest.skip("drop-in / reference binaries not built (need the reference sources)")
+    _run(exe, str(tmp_path / "ours"), 1, "dump_every 50\ndump_stride 10\n")
+    _run(REF_BIN, str(tmp_path / "ref"), 1)
+    ours = sorted(os.listdir(tmp_path / "ours" / "dumps"), key=lambda s: int(s[:-4]))
+    assert ours == ["0.txt", "50.txt", "100.txt", "150.txt", "200.txt"]
+    tol = np.array([1.01e-5] + [1.01e-3] * 6)
+    for name in ours:
+        ia, ta, a = _load(tmp_path / "ours" / "dumps" / name)
+        ib, tb, b = _load(tmp_path / "ref" / "dumps" / name)
+        if name == "0.txt":
+            # written by the reference's own init path before any step: the full array
+            assert len(ia) == len(ib)
+            continue
+        alive = [k for k, t in enumerate(tb) if t == "Alive"]
+        ghosts = [k for k, t in enumerate(tb) if t != "Alive"]
+        rows = alive[::10] + ghosts
+        assert len(ia) == len(rows) and ta == [tb[k] for k in rows]
+        assert ia[:len(alive[::10])] == [ib[k] for k in alive[::10]]      # alive ids; ghost ids are allocation artefacts
+        d = np.abs(a - b[rows])
+        lim = np.maximum(tol, 1e-9 * np.abs(b[rows]))
+        assert (d <= lim).all(), name
