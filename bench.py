@@ -50,6 +50,12 @@ WORKLOADS = {
     "colliding_streams_isothermal_fixedh_n1m": (1_000_000, 0, False),         # configs[1]
     "colliding_streams_adiabatic_varh_n256m": (256_000_000, 1, True),         # configs[4]: per GPU with --scaling weak
     "colliding_streams_adiabatic_varh_n1m": (1_000_000, 1, True),
+    # synthetic developed start state (sphb_init_developed): the exact solution of the same problem at t* = 0.5 — wall
+    # rarefactions, undisturbed streams, two shocks around compressed gas — sampled with equal-mass particles
+    # (second start state of config 5); every particle is being accelerated from the first step
+    "colliding_streams_adiabatic_varh_developed_n64m": (64_000_000, 1, True, "developed"),
+    "colliding_streams_adiabatic_varh_developed_n16m": (16_000_000, 1, True, "developed"),
+    "colliding_streams_adiabatic_varh_developed_n256m": (256_000_000, 1, True, "developed"),
     "colliding_streams_adiabatic_varh_n64m_pow2": (64 * 1024 * 1024, 1, True),    # best case of the ordered sweep
     "colliding_streams_adiabatic_varh_n16m_pow2": (16 * 1024 * 1024, 1, True),
     "colliding_streams_isothermal_fixedh_n1m_pow2": (1024 * 1024, 0, False),
@@ -126,18 +132,31 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------
 # CPU legs (the only places bench.py may execute oracle/)
 
-def cpu_port_baseline(pc, varh, sample_n=600_001, steps=4):
-    """The O(N k) plain-C port (oracle/sph_oracle.c), one thread, same generator at sample_n."""
+def cpu_port_baseline(pc, varh, sample_n=600_001, steps=4, init="lattice"):
+    """The O(N k) plain-C port (oracle/sph_oracle.c), one thread, same generator at sample_n.  For the developed
+    workload the start state of the sample comes from the same generator as the GPU arm's (sphb_init_developed at
+    sample_n, downloaded): the port is timed on it, it does not produce it."""
     from oracle.sph_oracle import Oracle
     kw = workload_kwargs(sample_n, pc, varh)
-    o = Oracle(**kw)
+    if init == "developed":
+        from sph_b200 import Config, Simulation
+        g = Simulation(Config(n_part=sample_n, mass=kw["mass"], pressure_calc=pc, t_i=kw["t_i"]), variable_h=varh,
+                       fixed_h=kw["constant_h"])
+        g.init_developed(0.5)
+        f, _, ng = g.fields()
+        g.close()
+        o = Oracle(**kw, init=False)
+        o.set_state(f, ng)
+    else:
+        o = Oracle(**kw)
     t0 = time.perf_counter()
     o.step(steps)
     dt = time.perf_counter() - t0
     o.close()
     return {"value": sample_n * steps / dt, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": "same lattice generator at N=%d, %d steps after t=0 set-up, %.1f s; O(N k) port of the "
-                      "reference (the literal reference is O(N^3) and cannot run at this N)" % (sample_n, steps, dt)}
+            "sample": "same %s at N=%d, %d steps, %.1f s; O(N k) port of the "
+                      "reference (the literal reference is O(N^3) and cannot run at this N)" % (
+                          "developed start state" if init == "developed" else "lattice generator", sample_n, steps, dt)}
 
 
 def _ref_worker(args):
@@ -276,7 +295,10 @@ def run_ours(args, name, n, pc, varh):
     else:
         stream = torch.cuda.Stream()
         sim.set_stream(stream.cuda_stream)
-    sim.init_lattice()
+    if args.init == "developed":
+        sim.init_developed(0.5)
+    else:
+        sim.init_lattice()
 
     def barrier():
         if world > 1:
@@ -437,7 +459,7 @@ def run_ours(args, name, n, pc, varh):
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_port_baseline(pc, varh)
+        cpu = cpu_port_baseline(pc, varh, init=args.init)
 
     if world > 1:
         dist.barrier()
@@ -449,6 +471,8 @@ def run_ours(args, name, n, pc, varh):
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": name, "n_particles": n, "pressure_calc": "adiabatic" if pc == 1 else "isothermal",
                        "smoothing_length": "variable (Newton/bisection per particle)" if varh else "fixed, 5 spacings",
+                       "start_state": ("synthetic developed state: exact colliding-streams solution at t* = 0.5, equal-mass sampling "
+                                       "(sphb_init_developed)" if args.init == "developed" else "t = 0 lattice of init_particles (setup.cpp:143-228)"),
                        "lattice": ("N = 2^k: dyadic positions, undisturbed streams feel no kick: best case of the ordered sweep"
                                    if (n // world if args.scaling == "weak" else n) & ((n // world if args.scaling == "weak" else n) - 1) == 0
                                    else "generic N: every particle feels a rounding-level kick, the ordered sweep has work everywhere"),
@@ -492,7 +516,8 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
-    n, pc, varh = WORKLOADS[args.workload]
+    n, pc, varh = WORKLOADS[args.workload][:3]
+    args.init = WORKLOADS[args.workload][3] if len(WORKLOADS[args.workload]) > 3 else "lattice"
     name = args.workload
     if args.n:
         n = args.n

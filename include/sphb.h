@@ -158,6 +158,13 @@ int sphb_download_counts(sphb_handle *h, int *newton_iters, int *neighbours, int
  * adiabatic pre-pass, ghosts, t = 0 density / acceleration / du_dt — all on the device. */
 int sphb_init_lattice(sphb_handle *h);
 
+/* No counterpart in the reference (its only start state is the lattice): a synthetic DEVELOPED state of the same
+ * colliding adiabatic streams — the exact solution at time t_star (gas at rest at the walls, rarefaction fans, the
+ * undisturbed streams, two outward shocks around shocked gas at rest) sampled with equal-mass particles, then ghosts,
+ * density / root-find (ghosts included) and forces as in init_particles.  For benchmarks and tests on a state in which
+ * every particle is being accelerated; t_star < ~0.55 with the default limit (the fans must not have met the shocks). */
+int sphb_init_developed(sphb_handle *h, double t_star);
+
 /* Replaces DensityCalculator::operator() (calculators.cpp:33-55) and rootfind_h /
  * calc_density / calc_omega (smoothing_length.cpp:64-91,191-259) for every alive particle
  * (and every ghost when include_ghosts != 0 — the t = 0 case, setup.cpp:218-220). */
@@ -245,6 +252,8 @@ int sphb_slab_forces(sphb_handle *h);
 int sphb_nccl_unique_id(void *out128);
 int sphb_slab_comm_init(sphb_handle *h, const void *unique_id128);
 int sphb_slab_init_particles(sphb_handle *h);   /* init_particles, setup.cpp:143-228, across the slabs */
+int sphb_slab_init_developed(sphb_handle *h, double t_star);   /* sphb_init_developed across the slabs */
+int sphb_slab_init_developed_fill(sphb_handle *h, double t_star);  /* its first phase only: this handle's particles, no ghosts */
 int sphb_slab_step(sphb_handle *h, int nsteps); /* step_forward, sph_simulation.cpp:55-108, across the slabs */
 int sphb_slab_rounds_last(const sphb_handle *h);/* ITERATE exchanges the last step needed */
 

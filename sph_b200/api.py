@@ -147,6 +147,9 @@ def load_library():
     L.sphb_download_fields.argtypes = [p, p, p, i, ip, ip]
     L.sphb_download_counts.argtypes = [p, p, p, i]
     L.sphb_init_lattice.argtypes = [p]
+    L.sphb_init_developed.argtypes = [p, d]
+    L.sphb_slab_init_developed.argtypes = [p, d]
+    L.sphb_slab_init_developed_fill.argtypes = [p, d]
     L.sphb_density.argtypes = [p, i]
     L.sphb_forces.argtypes = [p]
     L.sphb_omega.argtypes = [p, p, i]
@@ -294,6 +297,10 @@ class Simulation:
     # ---- the path
     def init_lattice(self):
         self._check(self.L.sphb_init_lattice(self.h))
+
+    def init_developed(self, t_star=0.5):
+        """Synthetic developed start state (sphb_init_developed): the exact colliding-streams solution at t_star."""
+        self._check(self.L.sphb_init_developed(self.h, float(t_star)))
 
     def density(self, include_ghosts=False):
         self._check(self.L.sphb_density(self.h, int(include_ghosts)))

@@ -1315,6 +1315,68 @@ int sphb_slab_prepass(sphb_handle *H) {
     return SPHB_OK;
 }
 
+// Synthetic developed start state (see k_developed): particles of this handle only, no ghosts, densities as sampled
+int sphb_slab_init_developed_fill(sphb_handle *H, double t_star) {
+    if (!H) return SPHB_ERR_INVALID;
+    if (H->cfg.pressure_calc != SPHB_ADIABATIC || !(t_star > 0.0)) {
+        H->err = "the developed start state is defined for adiabatic runs and t_star > 0";
+        return SPHB_ERR_INVALID;
+    }
+    CK(cudaSetDevice(H->device));
+    const long long n = H->slab ? H->n_global : (long long)H->na;
+    if (n < 2) { H->err = "need at least 2 particles"; return SPHB_ERR_INVALID; }
+    DevelopedArgs D;
+    D.x = H->x; D.v = H->v; D.u = H->u; D.a = H->a; D.du = H->du; D.h = H->h; D.rho = H->rho; D.P = H->P; D.m = H->m;
+    D.idx = H->idx; D.slot_id = H->slot_id; D.pad = H->pad; D.na = H->na; D.i0 = H->slab ? H->idx_base : 0; D.n_global = n;
+    D.limit = H->cfg.limit; D.mass = H->cfg.mass; D.hfac = H->cfg.h_factor; D.t = t_star;
+    const double L = H->cfg.limit, g = kGamma;
+    D.Mhalf = 0.5 * (double)n * H->cfg.mass;
+    D.rho0 = D.Mhalf / L;                              // the lattice's density
+    D.P0 = (g - 1) * (1 / (g - 1)) * D.rho0;           // u0 = 1 / (gamma - 1), setup.cpp:171-172
+    D.c0 = std::sqrt(g * D.P0 / D.rho0);
+    D.v0 = D.c0;                                       // the adiabatic streams start at +-c_s (setup.cpp:197-201)
+    D.K = D.v0 - 3.0 * D.c0;                           // v - 2 c / (gamma - 1)
+    D.c_w = D.c0 - D.v0 / 3.0;
+    const double rw = D.c_w / D.c0;
+    D.rho_w = D.rho0 * rw * rw * rw;
+    D.P_w = D.P0 * rw * rw * rw * rw * rw;
+    // shock: rho0 (v0 + S) = rho1 S,  P1 = P0 + rho0 (v0 + S) v0,  e1 - e0 = (P1 + P0) / 2 (1/rho0 - 1/rho1)
+    auto residual = [&](double S, double *rho1, double *P1) {
+        const double r1 = D.rho0 * (D.v0 + S) / S, p1 = D.P0 + D.rho0 * (D.v0 + S) * D.v0;
+        if (rho1) { *rho1 = r1; *P1 = p1; }
+        return p1 / ((g - 1) * r1) - D.P0 / ((g - 1) * D.rho0) - 0.5 * (p1 + D.P0) * (1 / D.rho0 - 1 / r1);
+    };
+    double lo = 1e-9, hi = 100.0;
+    for (int it = 0; it < 200; it++) {
+        const double mid = 0.5 * (lo + hi);
+        if ((residual(lo, nullptr, nullptr) > 0) == (residual(mid, nullptr, nullptr) > 0)) lo = mid; else hi = mid;
+    }
+    D.S = 0.5 * (lo + hi);
+    residual(D.S, &D.rho1, &D.P1);
+    D.x_head = (D.v0 + D.c0) * t_star;
+    if (D.x_head + D.S * t_star >= L) { H->err = "t_star too late: the rarefaction has met the shock"; return SPHB_ERR_INVALID; }
+    D.M1 = D.rho_w * D.c_w * t_star;
+    D.M2 = D.M1 + D.rho0 * t_star * (std::pow(D.c0, 4) - std::pow(D.c_w, 4)) / std::pow(D.c0, 3);
+    D.M3 = D.M2 + D.rho0 * (L - D.S * t_star - D.x_head);
+    H->uniform_mass = true;
+    H->m0 = H->cfg.mass;
+    k_developed<<<nblk(H->na, 256), 256, 0, H->stream>>>(D);
+    H->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemsetAsync(H->d_ctl, 0, sizeof(Ctl), H->stream));   // no ghosts yet
+    H->ghost_in_half = false;
+    return slab_flags(H);
+}
+
+int sphb_init_developed(sphb_handle *H, double t_star) {
+    if (!H) return SPHB_ERR_INVALID;
+    if (H->slab) { H->err = "x-slab runs initialise phase by phase (sphb_slab_*), with halo exchanges in between"; return SPHB_ERR_INVALID; }
+    TRY(sphb_slab_init_developed_fill(H, t_star));
+    TRY(sphb_ghosts(H, nullptr));
+    TRY(sphb_density(H, 1));
+    return sphb_forces(H);
+}
+
 int sphb_init_lattice(sphb_handle *H) {
     if (!H) return SPHB_ERR_INVALID;
     if (H->slab) { H->err = "x-slab runs initialise phase by phase (sphb_slab_*), with halo exchanges in between"; return SPHB_ERR_INVALID; }
@@ -1505,6 +1567,19 @@ int sphb_slab_init_particles(sphb_handle *H) {
         TRY(sphb_density(H, 0));
         TRY(sphb_slab_prepass(H));
     }
+    TRY(sphb_ghosts(H, nullptr));
+    TRY(native_exchange(H, MSG_BASE));
+    TRY(sphb_density(H, 1));
+    TRY(sphb_slab_records(H));
+    TRY(native_exchange(H, MSG_RECORDS));
+    return sphb_slab_forces(H);
+}
+
+// the developed start state across the slabs
+int sphb_slab_init_developed(sphb_handle *H, double t_star) {
+    if (!H || !H->comm) return SPHB_ERR_INVALID;
+    CK(cudaSetDevice(H->device));
+    TRY(sphb_slab_init_developed_fill(H, t_star));
     TRY(sphb_ghosts(H, nullptr));
     TRY(native_exchange(H, MSG_BASE));
     TRY(sphb_density(H, 1));

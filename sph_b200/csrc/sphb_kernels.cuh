@@ -1825,6 +1825,59 @@ __global__ void k_lattice(LatticeArgs A) {
     A.idx[s] = (unsigned)(A.i0 + i);
     A.slot_id[i] = (int)(A.i0 + i);
 }
+// A DEVELOPED state of the same problem (synthetic; no counterpart in the reference, whose only start state is the
+// lattice): the exact solution of the colliding adiabatic streams at time t, sampled with equal-mass particles.  Per
+// half domain, from the wall inwards: gas at rest next to the wall (rho_w, c_w), a centred rarefaction fan
+// (v + c = xi / t, v - 3 c = K for gamma = 5/3), the undisturbed stream (rho0, v0, c0), and the shocked gas at rest
+// (rho1, P1) behind a shock moving outwards at speed S.  Particle i sits where the cumulative mass from the left wall is
+// (i + 1/2) m; the right half is the mirror image.  h = h_factor m / rho, u = P / ((gamma - 1) rho).
+struct DevelopedArgs {
+    double *x, *v, *u, *a, *du, *h, *rho, *P, *m;
+    unsigned *idx;
+    int *slot_id;
+    int pad, na;
+    long long i0, n_global;
+    double limit, mass, hfac, t;
+    double rho0, P0, v0, c0, K, c_w, rho_w, P_w, S, rho1, P1;
+    double M1, M2, M3, Mhalf;      // cumulative mass at the end of the wall region, the fan, the undisturbed stream; half the total
+    double x_head;                 // where the fan ends (distance from the wall)
+};
+__global__ void k_developed(DevelopedArgs A) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= A.na) return;
+    const int s = A.pad + i;
+    const long long gi = A.i0 + i;
+    const double mu = ((double)gi + 0.5) * A.mass;
+    const bool right = mu > A.Mhalf;
+    const double M = right ? 2.0 * A.Mhalf - mu : mu;       // mass between the particle and ITS wall
+    double d, vel, rho, P;                                  // d = distance from that wall
+    if (M <= A.M1) {
+        d = M / A.rho_w; vel = 0.0; rho = A.rho_w; P = A.P_w;
+    } else if (M <= A.M2) {
+        // fan: mass(c) = M1 + rho0 t (c^4 - c_w^4) / c0^3
+        const double c4 = fma((M - A.M1), (A.c0 * A.c0 * A.c0) / (A.rho0 * A.t), (A.c_w * A.c_w) * (A.c_w * A.c_w));
+        const double c = sqrt(sqrt(c4));
+        d = A.t * (4.0 * c + A.K);
+        vel = (4.0 * c + A.K) - c;
+        const double r = c / A.c0, r3 = r * r * r;
+        rho = A.rho0 * r3; P = A.P0 * r3 * r * r;
+    } else if (M <= A.M3) {
+        d = A.x_head + (M - A.M2) / A.rho0; vel = A.v0; rho = A.rho0; P = A.P0;
+    } else {
+        d = (A.limit - A.S * A.t) + (M - A.M3) / A.rho1; vel = 0.0; rho = A.rho1; P = A.P1;
+        d = fmin(d, A.limit);
+    }
+    A.x[s] = right ? A.limit - d : d - A.limit;
+    A.v[s] = right ? -vel : vel;
+    A.u[s] = P / ((kGamma - 1) * rho);
+    A.h[s] = A.hfac * A.mass / rho;
+    A.rho[s] = rho;
+    A.P[s] = P;
+    A.m[s] = A.mass;
+    A.a[s] = 0; A.du[s] = 0;
+    A.idx[s] = (unsigned)gi;
+    A.slot_id[i] = (int)gi;
+}
 __global__ void k_prepass(const double *x, double *v, const double *u, const double *rho, double *P, int pad,
                           int na) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;

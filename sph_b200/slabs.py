@@ -229,6 +229,20 @@ class SlabSimulation:
         with self._torch.cuda.stream(self.stream):
             self._step(nsteps)
 
+    def init_developed(self, t_star=0.5):
+        """sphb_init_developed across the slabs."""
+        with self._torch.cuda.stream(self.stream):
+            for r in self.ranks:
+                r._check(r.L.sphb_slab_init_developed_fill(r.h, float(t_star)))
+            for r in self.ranks:
+                r.ghosts()
+            self._exchange(MSG_BASE)
+            for r in self.ranks:
+                r.density(include_ghosts=True)
+            self._all("records")
+            self._exchange(MSG_RECORDS)
+            self._all("forces")
+
     def _init_lattice(self):
         adiabatic = self.ranks[0].config.pressure_calc == 1
         self._all("init_lattice")
@@ -353,6 +367,10 @@ class NativeSlabSimulation:
     def init_lattice(self):
         r = self.ranks[0]
         r._check(r.L.sphb_slab_init_particles(r.h))
+
+    def init_developed(self, t_star=0.5):
+        r = self.ranks[0]
+        r._check(r.L.sphb_slab_init_developed(r.h, float(t_star)))
 
     def step(self, nsteps=1):
         r = self.ranks[0]

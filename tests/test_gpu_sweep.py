@@ -115,3 +115,37 @@ def test_auto_mode_is_the_same_bits_and_keeps_the_serial_sweep_on_a_generic_latt
     f, g, c = _run(kw, 6)
     assert c.sweep_steps == 6
     assert g == gref and np.array_equal(f, ref)
+
+
+def test_developed_start_state_against_the_oracle_and_between_strategies():
+    """sphb_init_developed: the exact two-shock / two-rarefaction state at t* = 0.5, N = 100,001.  Mass, the jump
+    conditions and the symmetry of the sampled state are checked directly; then the state is handed to the oracle and
+    both advance 5 steps (every particle is accelerated here: no quiet streams), in both sweep strategies."""
+    from oracle.sph_oracle import Oracle
+    n = 100_001
+    kw = _kw(n)
+    runs = {}
+    for mode in (WORKLIST, SERIAL):
+        sim = _sim(kw, sweep_mode=mode)
+        sim.init_developed(0.5)
+        f0, t0, g0 = sim.fields()
+        sim.step(5)
+        runs[mode] = (f0, g0, sim.fields()[0], sim.counters())
+        sim.close()
+    f0, g0, f5, c = runs[SERIAL]
+    assert np.array_equal(runs[WORKLIST][2], f5) and np.array_equal(runs[WORKLIST][0], f0)
+    x, v, rho, P, u, h = (f0[:n, COLS[k]] for k in ("pos", "vel", "density", "pressure", "u", "h"))
+    assert np.all(np.diff(x) > 0) and abs(x[n // 2]) < 1e-12 and np.allclose(x, -x[::-1], atol=1e-12) and np.allclose(v, -v[::-1], atol=1e-12)
+    mid = slice(n // 2 - 2000, n // 2 - 200)                     # shocked gas at rest: rho1 / rho0 = 2.1514..., P1 = 4.1142...
+    assert abs(np.median(rho[mid]) / 2.151409 - 1) < 2e-3 and np.abs(v[mid]).max() < 1e-12
+    assert abs(np.median((2.0 / 3.0) * u[mid] * rho[mid]) / 4.114236 - 1) < 2e-3
+    wall = slice(200, 2000)                                      # gas at rest at the wall: rho_w = (2/3)^3 rho0
+    assert abs(np.median(rho[wall]) / (8.0 / 27.0) - 1) < 2e-3
+    o = Oracle(**kw, init=False)
+    o.set_state(f0, g0)
+    o.step(5)
+    ref = o.fields()
+    assert ref.shape == f5.shape
+    for col in ("pos", "vel", "h", "u", "density"):
+        assert scaled_err(f5[:n, COLS[col]], ref[:n, COLS[col]]) < 1e-10, col
+    assert c.sweep_steps == 5
