@@ -955,6 +955,9 @@ __global__ void __launch_bounds__(kTile, 3) k_force_refine(SweepArgs A, int max_
 // and reaches the same fixed point.  Both kernels evaluate a particle with the same functions in the same
 // order, so an unflagged particle passes that evaluation unchanged.
 constexpr int kSweepThreads = 128;
+#ifndef SPHB_SWEEP_V
+#define SPHB_SWEEP_V 1    // build-time experiments: 1 = prefetch during the chain (measured: -5 %), 2 = two right-hand pairs per round (slower: spills)
+#endif
 
 struct SerialArgs {
     SweepArgs S;
@@ -1043,7 +1046,9 @@ __global__ void __launch_bounds__(kSweepThreads, G == 8 ? 4 : 3) k_force_sweep(S
 #pragma unroll 1
     for (int c = 0; c < nch; c++) {
         const int bc = c % 3, bp = (c + 2) % 3, bn = (c + 1) % 3;
+#if !(SPHB_SWEEP_V & 1)
         const Pre nx = fetch(c + 2);                 // replaces chunk c - 1 once phase P is done with it
+#endif
         const int s = st + c * G + gl;
         const int me = bc * G + gl;
         const unsigned idxi = S.idx[me];
@@ -1128,6 +1133,37 @@ __global__ void __launch_bounds__(kSweepThreads, G == 8 ? 4 : 3) k_force_sweep(S
                 }
             }
             // right-hand side, farthest first: old state
+#if (SPHB_SWEEP_V & 2)
+            // two neighbours per round: their evaluations are independent and the compiler can overlap the two dependent
+            // FP64 chains (the sums still receive the farther one first)
+            int d = dR;
+#pragma unroll 1
+            for (; d >= 2; d -= 2) {
+                const int rp0 = rpos(d), rp1 = rpos(d - 1);
+                if (S.idx[rp0] < o.idx || S.idx[rp1] < o.idx) flag = true;
+                const double2 hc0 = S.hcB[rp0], rk0 = S.rkB[rp0], hc1 = S.hcB[rp1], rk1 = S.rkB[rp1];
+                Rec r0, r1;
+                r0.h = hc0.x; r0.c5 = hc0.y; r0.rho = rk0.x; r0.kap = rk0.y;
+                r1.h = hc1.x; r1.c5 = hc1.y; r1.rho = rk1.x; r1.kap = rk1.y;
+                PairK k0, k1;
+                const bool ok0 = pair_geom<ADIA>(o, S.x[rp0] - o.x, -1.0, r0, k0);
+                const bool ok1 = pair_geom<ADIA>(o, S.x[rp1] - o.x, -1.0, r1, k1);
+                if (ok0) { pair_apply<ADIA, true>(o, k0, S.vB[rp0], S.uB[rp0], 0.0, aR, eR); npairs_tot++; }
+                if (ok1) { pair_apply<ADIA, true>(o, k1, S.vB[rp1], S.uB[rp1], 0.0, aR, eR); npairs_tot++; }
+            }
+            if (d == 1) {
+                const int rp = rpos(1);
+                if (S.idx[rp] < o.idx) flag = true;
+                const double2 hc = S.hcB[rp], rk = S.rkB[rp];
+                Rec rj;
+                rj.h = hc.x; rj.c5 = hc.y; rj.rho = rk.x; rj.kap = rk.y;
+                PairK pk;
+                if (pair_geom<ADIA>(o, S.x[rp] - o.x, -1.0, rj, pk)) {
+                    pair_apply<ADIA, true>(o, pk, S.vB[rp], S.uB[rp], 0.0, aR, eR);
+                    npairs_tot++;
+                }
+            }
+#else
 #pragma unroll 1
             for (int d = dR; d >= 1; d--) {
                 const int rp = rpos(d);
@@ -1141,13 +1177,19 @@ __global__ void __launch_bounds__(kSweepThreads, G == 8 ? 4 : 3) k_force_sweep(S
                     npairs_tot++;
                 }
             }
+#endif
         }
         __syncwarp(gmask);                           // everybody is done with chunk c - 1
+#if (SPHB_SWEEP_V & 1)
+        // the loads of chunk c + 2 fly while the chain runs (its registers are not live during phase P)
+        const Pre nx = fetch(c + 2);
+#else
         {
             const int q = bp * G + gl;
             S.x[q] = nx.x; S.idx[q] = nx.idx; S.hcA[q] = nx.hcA; S.rkA[q] = nx.rkA; S.hcB[q] = nx.hcB; S.rkB[q] = nx.rkB;
             S.vB[q] = nx.vB; S.uB[q] = nx.uB; S.vA[q] = nx.vB; S.uA[q] = nx.uB;
         }
+#endif
         // the chain
 #pragma unroll
         for (int t = 0; t < G - 1; t++) {
@@ -1170,6 +1212,13 @@ __global__ void __launch_bounds__(kSweepThreads, G == 8 ? 4 : 3) k_force_sweep(S
                 }
             }
         }
+#if (SPHB_SWEEP_V & 1)
+        {
+            const int q = bp * G + gl;
+            S.x[q] = nx.x; S.idx[q] = nx.idx; S.hcA[q] = nx.hcA; S.rkA[q] = nx.rkA; S.hcB[q] = nx.hcB; S.rkB[q] = nx.rkB;
+            S.vB[q] = nx.vB; S.uB[q] = nx.uB; S.vA[q] = nx.vB; S.uA[q] = nx.uB;
+        }
+#endif
         // every lane's left-hand sums are complete now (lane t's were when it was broadcast: same inputs, same bits)
         double my_a = (0.0 - aL) + aR, my_e = (0.0 + eL) - eR;
         my_a *= A.m0; my_e *= A.m0;
