@@ -97,6 +97,16 @@ __device__ __forceinline__ double clamp2(double t) { return t + fabs(t); }   // 
 // the outer shell costs 4 FP64 operations here, not 15.  Neighbouring lanes hold neighbouring
 // particles with nearly the same h and spacing, so the branches rarely diverge.
 __device__ __forceinline__ double dpoly_from(double t1, double r, double h, double k2, double k3, int hi_eps) {
+#ifdef SPHB_DPOLY_BRANCHFREE
+    // experiment: all three pieces unconditionally, clamped with s = t + |t| = 2 max(t, 0) (exact); straight-line code
+    // that the scheduler can overlap with the reciprocal chain of the pair
+    (void)hi_eps;
+    const double s1 = clamp2(t1), s2 = clamp2(fma(k2, h, -r)), s3 = clamp2(fma(k3, h, -r));
+    double q = (s1 * s1) * s1;
+    q = fma(-5.0, (s2 * s2) * s2, q);
+    q = fma(10.0, (s3 * s3) * s3, q);
+    return 0.125 * q;
+#endif
     double p = 0.0;
     if (__double2hiint(t1) >= hi_eps) {
         p = (t1 * t1) * t1;
