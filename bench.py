@@ -281,10 +281,20 @@ def run_ours(args, name, n, pc, varh):
         if world == 1 and args.gpus > 1:
             raise SystemExit("bench.py --gpus %d must be launched under torch.distributed.run" % args.gpus)
 
+    limit = 2.0
     if args.scaling == "weak":
-        n = n * world            # the named N is per GPU; 8 x 256,000,000 stays below 2^31 (the index field)
+        # The named N is per GPU (8 x 256,000,000 stays below 2^31, the index field), and the TUBE grows with the GPU
+        # count (limit = 2 x GPUs): spacing, smoothing lengths and time step per GPU stay what they are on one GPU.
+        # Packing 2e9 particles into the reference's 4 units of length is not an option: h = 2 spacings = 4e-9 would lie
+        # below the reference's absolute CALC_EPSILON = 1e-8 (define.hpp:25), which its ghost set-up
+        # (ghost_particles.cpp:37-43) and root-find bracket (smoothing_length.cpp:223-230,165) treat as "zero".
+        n = n * world
+        limit = 2.0 * world
     kw = workload_kwargs(n, pc, varh)
-    cfg = Config(n_part=n, mass=kw["mass"], pressure_calc=pc, t_i=kw["t_i"])
+    kw["mass"] *= limit / 2.0
+    kw["t_i"] *= limit / 2.0
+    kw["constant_h"] *= limit / 2.0
+    cfg = Config(n_part=n, mass=kw["mass"], pressure_calc=pc, limit=limit, t_i=kw["t_i"])
     from sph_b200.slabs import make_simulation   # 1 rank: a plain Simulation; >1: this rank's x-slab
     sim = make_simulation(cfg, variable_h=varh, fixed_h=kw["constant_h"], device=local, rank=rank, world=world,
                           halo_count=args.halo, native=not args.torch_exchange, sweep_rel_tol=args.sweep_tol,
@@ -416,9 +426,9 @@ def run_ours(args, name, n, pc, varh):
 
     # ---- end to end through the C-ABI with HOST buffers, every step: upload + step + download
     e2e = None
-    if True:
+    if args.e2e_steps > 0:
         # every rank moves ITS particles (the whole set on one GPU, its slab otherwise) through host memory
-        e2e_steps = max(1, min(args.steps, 3))
+        e2e_steps = max(1, min(args.steps, args.e2e_steps))
         hs = sim if world == 1 else sim.ranks[0]     # the object that owns this rank's handle
         n_loc = n_local
         nbuf = n_loc + 2 * 4096
@@ -478,7 +488,7 @@ def run_ours(args, name, n, pc, varh):
                                    else "generic N: every particle feels a rounding-level kick, the ordered sweep has work everywhere"),
                        "order": ("reference (index-ordered in-place sweep, bitwise fixed point)" if args.sweep_tol == 0 else
                                  "reference (index-ordered in-place sweep, converged to %.1e relative)" % args.sweep_tol), "sweeps_per_step": sweeps_mean,
-                       "n_particles_per_gpu": n // world,
+                       "n_particles_per_gpu": n // world, "limit": limit,
                        "parallelism": ("x-slabs x%d, %d-particle halos over ncclSend/ncclRecv, %d ITERATE exchanges in the last step"
                                        % (world, args.halo, rounds_last)) if world > 1 else "single GPU",
                        "sweep": {"serial_steps": c2.sweep_steps, "group": c2.sweep_group, "segment": c2.sweep_segment,
@@ -502,6 +512,7 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--n", type=int, default=0, help="override the particle count of the workload")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=3, help="steps of the end-to-end (host buffer) leg; 0 skips it")
     ap.add_argument("--sweep-tol", type=float, default=0.0,
                     help="0 (default): the ordered sweep is iterated to its bitwise fixed point; > 0: relative tolerance")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],

@@ -1557,35 +1557,61 @@ int sphb_slab_comm_init(sphb_handle *H, const void *unique_id128) {
     return SPHB_OK;
 }
 
-// init_particles (setup.cpp:143-228) across the slabs, halo exchanges included
+// MAX over the ranks of a status code (one small all-reduce + host synchronisation): every rank returns the same status
+// from a collective entry point — a rank returning alone would leave the others waiting in the next exchange
+int agree_status(sphb_handle *H, int rc) {
+    H->h_flags[7] = rc;
+    CK(cudaMemcpyAsync(H->d_flags + 7, H->h_flags + 7, sizeof(int), cudaMemcpyHostToDevice, H->stream));
+    NK(g_nccl.AllReduce(H->d_flags + 7, H->d_flags + 7, 1, ncclInt32, ncclMax, H->comm, H->stream));
+    CK(cudaMemcpyAsync(H->h_flags + 7, H->d_flags + 7, sizeof(int), cudaMemcpyDeviceToHost, H->stream));
+    CK(cudaStreamSynchronize(H->stream));
+    const int agreed = H->h_flags[7];
+    if (agreed != SPHB_OK && rc == SPHB_OK) H->err = "another slab reported an error during set-up";
+    return agreed;
+}
+
+// init_particles (setup.cpp:143-228) across the slabs, halo exchanges included.  A device error on one rank does not
+// stop that rank's part in the exchanges that follow (the others would wait for ever): the first status is kept,
+// the phases go on, and the ranks agree on the status at the end.
 int sphb_slab_init_particles(sphb_handle *H) {
     if (!H || !H->comm) return SPHB_ERR_INVALID;
     CK(cudaSetDevice(H->device));
-    TRY(sphb_slab_init_lattice(H));
+    int rc = SPHB_OK;
+    auto keep = [&](int r) { if (rc == SPHB_OK && r != SPHB_OK) rc = r; };
+    std::string first_err;
+    auto note = [&]() { if (rc != SPHB_OK && first_err.empty()) first_err = H->err; };
+    keep(sphb_slab_init_lattice(H)); note();
     if (H->cfg.pressure_calc == SPHB_ADIABATIC) {
-        TRY(native_exchange(H, MSG_BASE));
-        TRY(sphb_density(H, 0));
-        TRY(sphb_slab_prepass(H));
+        keep(native_exchange(H, MSG_BASE)); note();
+        keep(sphb_density(H, 0)); note();
+        keep(sphb_slab_prepass(H)); note();
     }
-    TRY(sphb_ghosts(H, nullptr));
-    TRY(native_exchange(H, MSG_BASE));
-    TRY(sphb_density(H, 1));
-    TRY(sphb_slab_records(H));
-    TRY(native_exchange(H, MSG_RECORDS));
-    return sphb_slab_forces(H);
+    keep(sphb_ghosts(H, nullptr)); note();
+    keep(native_exchange(H, MSG_BASE)); note();
+    keep(sphb_density(H, 1)); note();
+    keep(sphb_slab_records(H)); note();
+    keep(native_exchange(H, MSG_RECORDS)); note();
+    keep(sphb_slab_forces(H)); note();
+    if (rc != SPHB_OK) H->err = first_err;
+    return agree_status(H, rc);
 }
 
-// the developed start state across the slabs
+// the developed start state across the slabs (status agreed like sphb_slab_init_particles)
 int sphb_slab_init_developed(sphb_handle *H, double t_star) {
     if (!H || !H->comm) return SPHB_ERR_INVALID;
     CK(cudaSetDevice(H->device));
-    TRY(sphb_slab_init_developed_fill(H, t_star));
-    TRY(sphb_ghosts(H, nullptr));
-    TRY(native_exchange(H, MSG_BASE));
-    TRY(sphb_density(H, 1));
-    TRY(sphb_slab_records(H));
-    TRY(native_exchange(H, MSG_RECORDS));
-    return sphb_slab_forces(H);
+    int rc = SPHB_OK;
+    std::string first_err;
+    auto keep = [&](int r) { if (rc == SPHB_OK && r != SPHB_OK) { rc = r; first_err = H->err; } };
+    keep(sphb_slab_init_developed_fill(H, t_star));
+    keep(sphb_ghosts(H, nullptr));
+    keep(native_exchange(H, MSG_BASE));
+    keep(sphb_density(H, 1));
+    keep(sphb_slab_records(H));
+    keep(native_exchange(H, MSG_RECORDS));
+    keep(sphb_slab_forces(H));
+    if (rc != SPHB_OK) H->err = first_err;
+    return agree_status(H, rc);
 }
 
 // SPHSimulation::step_forward (sph_simulation.cpp:55-108) on this rank's slab, nsteps times; every

@@ -342,13 +342,15 @@ __global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs
                     iters++;
                     if (df == 0.0) { raise(ctl, E_ZERO_DERIVATIVE, s); failed = true; break; }
                     const double xn = xcur - f / df;
-                    if (fabs(xn - xcur) <= kTinyStep * fabs(xn)) {
+                    if (UM && fabs(xn - xcur) <= kTinyStep * fabs(xn)) {
                         // The step did not move h beyond 1e-12 relative: this iteration passes the stop test
                         // (1e-4), and what GSL evaluates at xn is not used for another step.  The sums at xn
                         // equal the sums just taken at xcur to within 1e-12 (the density to ~1e-24 with its
                         // first-order term), five orders below the parity tolerance: do not walk the window
-                        // again.  (Iteration count, returned h and stop decision are exactly the reference's.)
-                        if (UM) rho_cur = fma(-dsum, xcur - xn, rho_cur);     // rho(xn) = rho(xcur) + drho/dh (xn - xcur)
+                        // again.  (Iteration count, returned h and stop decision are exactly the reference's.)  Uniform
+                        // masses only: there dsum IS d rho_i / dh; with unequal masses (rho_i carries m_i, dsum the m_j)
+                        // the window is simply walked again.
+                        rho_cur = fma(-dsum, xcur - xn, rho_cur);     // rho(xn) = rho(xcur) + drho/dh (xn - xcur)
                         xcur = xn;
                         cont = false;
                         tiny = true;
@@ -367,8 +369,11 @@ __global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs
                              ((~*((volatile unsigned long long *)&ctl->err_first)) >> 8) > (unsigned long long)(s + 1))) {
                     // bisection fallback on [1e-8, 2 limit], gsl_root_test_interval rel 1e-4
                     // (its bracket end 2*limit sums over the whole domain: a slab cannot evaluate it)
-                    if (ctl->halo_left | ctl->halo_right) raise(ctl, E_HALO, s);
+                    // ... and must not try: scanning 2*limit from here would walk the whole slab, per thread
+                    const bool in_slab = (ctl->halo_left | ctl->halo_right) != 0;
+                    if (in_slab) { raise(ctl, E_HALO, s); failed = true; }
                     atomicAdd(&ctl->fallbacks, 1ull);
+                    if (!in_slab) {
                     double xl = kEps, xh = 2 * A.limit, fl, fh, dfx, dsx;
                     int c2 = cnt;
                     SPHB_EVAL(xl, fl, dfx, dsx);
@@ -404,6 +409,7 @@ __global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs
                     (void)c2;
                     xcur = root;
                     SPHB_EVAL(xcur, f, df, dsum);
+                    }
                 }
                 if (xcur < 0) { raise(ctl, E_NEGATIVE_H, s); failed = true; }
                 hnew = xcur;
@@ -1435,6 +1441,13 @@ __global__ void __launch_bounds__(1024) k_ghost_build(GhostArgs G) {
         G.gorder[rank_k] = dest;
     }
     if (threadIdx.x == 0) { ctl->GL = GL; ctl->GR = GR; }
+    // Every scan assumes that [pad - GL, pad + na + GR) is x-sorted as a whole.  A particle outside the wall, or wide
+    // enough to be mirrored about the far wall, would put its ghost INSIDE the alive range: the scans would then stop
+    // early and drop pairs silently (the reference's all-pairs loops do not).  Refuse instead.
+    __syncthreads();
+    if (threadIdx.x == 0 && G.na > 0 &&
+        ((GL > 0 && G.x[G.pad - 1] > G.x[G.pad]) || (GR > 0 && G.x[G.pad + G.na] < G.x[G.pad + G.na - 1])))
+        raise(ctl, E_UNSORTED, GL > 0 && G.x[G.pad - 1] > G.x[G.pad] ? G.pad - 1 : G.pad + G.na);
 }
 
 // copy ghost (pad) entries of v,u between the half-kicked and the current arrays
