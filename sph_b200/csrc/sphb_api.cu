@@ -1550,7 +1550,12 @@ int sphb_slab_comm_init(sphb_handle *H, const void *unique_id128) {
         }
     TRY(dalloc(H, &H->d_flags, 8));
     CK(cudaMallocHost((void **)&H->h_flags, 8 * sizeof(int)));
-    CK(cudaStreamCreateWithFlags(&H->comm_stream, cudaStreamNonBlocking));
+    // the halo exchanges and the edge tiles run beside kernels that fill the whole GPU: without a higher priority their
+    // CTAs would only be scheduled when the interior kernel drains, and the exchange chain would follow it instead of hiding
+    // behind it
+    int prio_least = 0, prio_greatest = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
+    CK(cudaStreamCreateWithPriority(&H->comm_stream, cudaStreamNonBlocking, prio_greatest));
     for (cudaEvent_t *e : {&H->ev_kick, &H->ev_base, &H->ev_edge, &H->ev_rec})
         CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     CK(cudaStreamSynchronize(H->stream));

@@ -1017,7 +1017,11 @@ __global__ void __launch_bounds__(kSweepThreads, G == 8 ? 4 : 3) k_force_sweep(S
     const double Hb = __longlong_as_double((long long)ctl->hmax_bits);
     const double reach_glob = kRadius * Hb;
     const int seg_lo = A.pad + seg * K.L, seg_hi = min(seg_lo + K.L, A.pad + A.na);
-    const int st = (seg == 0) ? lo : max(lo, seg_lo - K.B);   // first slot this group looks at
+    const bool halo_l0 = ctl->halo_left != 0;
+    // first slot this group looks at.  Segment 0 starts at the wall ghosts; on a slab edge its burn-in is the
+    // neighbouring slab's halo, of which twice the usual burn-in is walked (not all of it: the launch is one wave of
+    // equally long segments there, and this group would finish last)
+    const int st = (seg == 0) ? (halo_l0 ? max(lo, A.pad - 2 * K.B) : lo) : max(lo, seg_lo - K.B);
     const int nch = (seg_hi - st + G - 1) / G;
     const bool halo_l = ctl->halo_left != 0, halo_r = ctl->halo_right != 0;
 
