@@ -155,7 +155,11 @@ int sphb_download_fields(sphb_handle *h, double *fields, int *type, int cap, int
 int sphb_download_counts(sphb_handle *h, int *newton_iters, int *neighbours, int cap);
 
 /* Replaces init_particles (setup.cpp:143-228): lattice, +-v0 / +-c_s streams, u0, h0,
- * adiabatic pre-pass, ghosts, t = 0 density / acceleration / du_dt — all on the device. */
+ * adiabatic pre-pass, ghosts, t = 0 density / acceleration / du_dt — all on the device.
+ * The GHOST records' acc and du_dt are 0 after this call.  In the reference they hold two values nothing ever reads:
+ * the pre-pass acceleration (computed from a `pressure` member that is still uninitialised there, setup.cpp:192-202)
+ * and a du_dt evaluated at the mirrored position (setup.cpp:223-226).  Every other ghost field equals the reference's;
+ * from the first step on ghosts are copies of their source and acc / du_dt are copied with them. */
 int sphb_init_lattice(sphb_handle *h);
 
 /* No counterpart in the reference (its only start state is the lattice): a synthetic DEVELOPED state of the same
