@@ -63,10 +63,10 @@ def _routing_worker(rank, world, port, q):
             ok &= bool((recv[RIGHT] == 10.0 * (rank + 1) - 1).all())
         else:
             ok &= bool((recv[RIGHT] == 0).all())
-        flag = torch.zeros(4, dtype=torch.int32)
+        flag = torch.zeros(6, dtype=torch.int32)
         # one rank saw a change, another an error code, each its own h maximum: everybody learns the maxima
-        ok &= agree_max(dist, flag, [13 if rank == 0 else 0, 0, 1 if rank == world - 1 else 0, 100 + rank]) == [13, 0, 1, 99 + world]
-        ok &= agree_max(dist, flag, [0, 0, 0, 0]) == [0, 0, 0, 0]
+        ok &= agree_max(dist, flag, [13 if rank == 0 else 0, 0, 1 if rank == world - 1 else 0, 100 + rank, 7 * rank, rank % 2]) == [13, 0, 1, 99 + world, 7 * (world - 1), 1 if world > 1 else 0]
+        ok &= agree_max(dist, flag, [0] * 6) == [0] * 6
         q.put((rank, ok))
     finally:
         dist.destroy_process_group()
