@@ -275,7 +275,7 @@ struct DensityArgs {
 // SLAB: pads may hold another slab's particles and the launch may cover a subset of the tiles
 template <bool VARH, bool UM, bool SLAB>
 #ifndef SPHB_DENS_BLOCKS
-#define SPHB_DENS_BLOCKS 6
+#define SPHB_DENS_BLOCKS 5   // 48 registers: measured 2.43 ms at 64 M against 2.68 (6 CTAs, 40 registers, 88 B of spills) and 2.56 (4 CTAs)
 #endif
 __global__ void __launch_bounds__(kTile, SPHB_DENS_BLOCKS) k_density(DensityArgs A) {
     __shared__ double sxs[kTile + 2 * kDHalo + 2];
