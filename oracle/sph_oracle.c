@@ -8,8 +8,8 @@
  * window of candidates that can be non-zero.  Skipping an exactly-zero term
  * does not change an IEEE sum, so in index_order_sums mode (terms accumulated
  * in ascending array index, like the reference) the results are bit-identical
- * to the reference's own strict build; tests/test_oracle_vs_reference.py
- * checks that in the build container.
+ * to the reference's own strict build; tests/test_oracle_golden.py checks that
+ * against fixtures those builds produced (tests/golden/make_golden.py).
  *
  * Reference map (all paths relative to /root/reference/):
  *   orc_w / orc_dw            sph/kernel.cpp:14-38, 40-64

@@ -113,3 +113,16 @@ def test_dropin_program_thinned_out_dumps(tmp_path):
         d = np.abs(a - b[rows])
         lim = np.maximum(tol, 1e-9 * np.abs(b[rows]))
         assert (d <= lim).all(), name
+
+
+def test_adaptors_rethrow_with_the_reference_exception_types():
+    """calculators.cpp:184 throws a POINTER to std::logic_error for a density below epsilon, ghost_particles.cpp:39
+    throws std::logic_error by value for a zero smoothing length: a host program written against the reference
+    catches exactly those.  sph_b200/adaptors/throw_probe.cpp provokes both through the adaptors' functors."""
+    exe = os.path.join(DROPIN, "throw_probe")
+    if not os.path.exists(exe):
+        pytest.skip("probe not built (needs the reference sources)")
+    res = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert res.returncode == 0, res.stdout
+    assert "pointer: Particle had density less than epsilon!" in res.stdout
+    assert "value: Ghost particle initialization: Particle had zero smoothing length!" in res.stdout
